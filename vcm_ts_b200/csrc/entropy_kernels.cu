@@ -1,0 +1,405 @@
+// vcm_ts_b200/csrc/entropy_kernels.cu -- fused entropy-parameter / quantise / scale-index /
+// likelihood epilogues of the dual-spatial-prior (checkerboard) coder.
+//
+//   vcm_dual_prior_pass0/1   common_model.py:82-217 (get_mask, process_with_mask,
+//                            forward_dual_prior, compress_dual_prior, decompress_dual_prior)
+//                            + entropy_models.py:264-268 (GaussianEncoder.build_indexes)
+//   vcm_round_latent         video_model.py:284,310 / image_model.py:63 (z_hat = round(z))
+//   vcm_symbols_to_latent    entropy_models.py:189-195 / :276-281 (decoded ints -> float tensor)
+//   vcm_latent_bits          common_model.py:51-69 (probs_to_bits, Laplace / Normal CDF)
+//   vcm_factorized_bits      common_model.py:71-73, entropy_models.py:54-73,105-117
+//   vcm_sq_err_sum           video_model.py:544-545
+//
+// The reference runs ~60 elementwise ATen launches per dual-prior call; here each checkerboard
+// pass is ONE kernel that reads (y, q_step, scales, means) once and writes int16 symbols, uint8
+// scale indexes (in the reference's NCHW coding order), the reconstruction and the spatial-prior
+// input.  Integer outputs are bit-exact for identical float inputs: division is IEEE (__fdiv_rn),
+// rounding is round-half-to-even (rintf == torch.round), masks multiply exactly as the reference.
+#include "common.cuh"
+
+namespace {
+
+inline int ew_grid(int64_t total) {
+  int64_t g = (total + 255) / 256;
+  return (int)(g > 148 * 16 ? 148 * 16 : (g < 1 ? 1 : g));
+}
+
+__device__ __forceinline__ uint8_t scale_index(float sc, float lmin, float lstep) {
+  const float s = fmaxf(sc, 1e-5f);
+  float v = __fdiv_rn(__fsub_rn(logf(s), lmin), lstep);
+  v = fminf(fmaxf(v, 0.f), 255.f);
+  return (uint8_t)(int)v;
+}
+
+__device__ __forceinline__ int16_t to_sym(float q) {
+  return (int16_t)(int)fminf(fmaxf(q, -32768.f), 32767.f);
+}
+
+template <typename T>
+__global__ void dual_prior_pass0_kernel(const vcm_dp_desc D, const T* __restrict__ y,
+                                        const T* __restrict__ fusion, T* __restrict__ params,
+                                        float* __restrict__ yq, int16_t* __restrict__ sym,
+                                        uint8_t* __restrict__ idx, float* __restrict__ y_q_full,
+                                        float* __restrict__ scales_full) {
+  const int C = D.C, Ch = D.C / 2;
+  const int64_t total = (int64_t)D.N * Ch * D.h * D.w;
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total;
+       i += (int64_t)gridDim.x * blockDim.x) {
+    const int wx = (int)(i % D.w);
+    int64_t r = i / D.w;
+    const int hy = (int)(r % D.h);
+    r /= D.h;
+    const int c = (int)(r % Ch);
+    const int n = (int)(r / Ch);
+    const int64_t pix = ((int64_t)n * D.h + hy) * D.w + wx;
+    const bool m0 = ((hy + wx) & 1) == 0;
+#pragma unroll
+    for (int k = 0; k < 2; ++k) {
+      const int cc = c + k * Ch;
+      const float qs = fmaxf(ld_as_float(fusion + pix * D.fusion_cstride + cc), 0.5f);
+      const float sc = ld_as_float(fusion + pix * D.fusion_cstride + C + cc);
+      const float mu = ld_as_float(fusion + pix * D.fusion_cstride + 2 * C + cc);
+      T* pp = params + pix * D.params_cstride;
+      st_from_float(pp + C + cc, mu);
+      st_from_float(pp + 2 * C + cc, sc);
+      st_from_float(pp + 3 * C + cc, qs);
+      const bool active = (k == 0) ? m0 : !m0;
+      float yhat = 0.f, q = 0.f;
+      if (D.mode == 0) {
+        const float v = __fdiv_rn(ld_as_float(y + pix * D.y_cstride + cc), qs);
+        yq[pix * C + cc] = v;
+        if (active) {
+          q = rintf(__fsub_rn(v, mu));
+          yhat = __fadd_rn(q, mu);
+          sym[i] = to_sym(q);
+          idx[i] = scale_index(sc, D.log_scale_min, D.log_scale_step);
+        }
+      } else if (D.mode == 1) {
+        if (active) idx[i] = scale_index(sc, D.log_scale_min, D.log_scale_step);
+      } else {
+        if (active) {
+          q = (float)sym[i];
+          yhat = __fadd_rn(q, mu);
+        }
+      }
+      if (D.mode != 1) {
+        st_from_float(pp + cc, yhat);
+        if (y_q_full) {
+          y_q_full[pix * C + cc] = q;
+          scales_full[pix * C + cc] = active ? sc : 0.f;
+        }
+      }
+    }
+  }
+}
+
+template <typename T>
+__global__ void dual_prior_pass1_kernel(const vcm_dp_desc D, const float* __restrict__ yq,
+                                        const T* __restrict__ prior, const T* __restrict__ params,
+                                        const float* __restrict__ q_outer, T* __restrict__ y_hat,
+                                        int16_t* __restrict__ sym, uint8_t* __restrict__ idx,
+                                        float* __restrict__ y_q_full, float* __restrict__ scales_full) {
+  const int C = D.C, Ch = D.C / 2;
+  const int64_t total = (int64_t)D.N * Ch * D.h * D.w;
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total;
+       i += (int64_t)gridDim.x * blockDim.x) {
+    const int wx = (int)(i % D.w);
+    int64_t r = i / D.w;
+    const int hy = (int)(r % D.h);
+    r /= D.h;
+    const int c = (int)(r % Ch);
+    const int n = (int)(r / Ch);
+    const int64_t pix = ((int64_t)n * D.h + hy) * D.w + wx;
+    const bool m0 = ((hy + wx) & 1) == 0;
+#pragma unroll
+    for (int k = 0; k < 2; ++k) {
+      const int cc = c + k * Ch;
+      const bool active = (k == 0) ? !m0 : m0;  // pass 1 codes the complementary positions
+      const float sc = ld_as_float(prior + pix * D.prior_cstride + k * C + c);
+      const float mu = ld_as_float(prior + pix * D.prior_cstride + k * C + Ch + c);
+      const T* pp = params + pix * D.params_cstride;
+      float part = 0.f, q = 0.f;
+      if (D.mode == 0) {
+        if (active) {
+          q = rintf(__fsub_rn(yq[pix * C + cc], mu));
+          part = __fadd_rn(q, mu);
+          sym[i] = to_sym(q);
+          idx[i] = scale_index(sc, D.log_scale_min, D.log_scale_step);
+        }
+      } else if (D.mode == 1) {
+        if (active) idx[i] = scale_index(sc, D.log_scale_min, D.log_scale_step);
+      } else {
+        if (active) {
+          q = (float)sym[i];
+          part = __fadd_rn(q, mu);
+        }
+      }
+      if (D.mode != 1) {
+        const float first = ld_as_float(pp + cc);
+        const float qs = ld_as_float(pp + 3 * C + cc);
+        float v = __fadd_rn(first, part);
+        v = __fmul_rn(v, qs);
+        v = __fmul_rn(v, __ldg(q_outer + (int64_t)n * C + cc));
+        st_from_float(y_hat + pix * D.yhat_cstride + cc, v);
+        if (y_q_full && active) {
+          y_q_full[pix * C + cc] = q;
+          scales_full[pix * C + cc] = sc;
+        }
+      }
+    }
+  }
+}
+
+template <typename T>
+__global__ void round_latent_kernel(const T* __restrict__ z, T* __restrict__ z_hat,
+                                    int16_t* __restrict__ sym, int N, int h, int w, int C, int z_cs,
+                                    int zhat_cs) {
+  const int64_t total = (int64_t)N * C * h * w;
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total;
+       i += (int64_t)gridDim.x * blockDim.x) {
+    const int wx = (int)(i % w);
+    int64_t r = i / w;
+    const int hy = (int)(r % h);
+    r /= h;
+    const int c = (int)(r % C);
+    const int n = (int)(r / C);
+    const int64_t pix = ((int64_t)n * h + hy) * w + wx;
+    const float q = rintf(ld_as_float(z + pix * z_cs + c));
+    st_from_float(z_hat + pix * zhat_cs + c, q);
+    if (sym) sym[i] = to_sym(q);
+  }
+}
+
+template <typename T>
+__global__ void symbols_to_latent_kernel(const int16_t* __restrict__ sym, T* __restrict__ z_hat,
+                                         int N, int h, int w, int C, int zhat_cs) {
+  const int64_t total = (int64_t)N * C * h * w;
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total;
+       i += (int64_t)gridDim.x * blockDim.x) {
+    const int wx = (int)(i % w);
+    int64_t r = i / w;
+    const int hy = (int)(r % h);
+    r /= h;
+    const int c = (int)(r % C);
+    const int n = (int)(r / C);
+    const int64_t pix = ((int64_t)n * h + hy) * w + wx;
+    st_from_float(z_hat + pix * zhat_cs + c, (float)sym[i]);
+  }
+}
+
+// ---- reductions (deterministic: fixed chunking, fixed shuffle tree, ordered final sum) ------
+constexpr int RED_CHUNK = 8192;
+
+__device__ __forceinline__ float block_sum_256(float v) {
+  __shared__ float ws[8];
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  if ((threadIdx.x & 31) == 0) ws[threadIdx.x >> 5] = v;
+  __syncthreads();
+  float t = 0.f;
+  if (threadIdx.x == 0)
+    for (int k = 0; k < 8; ++k) t += ws[k];
+  return t;  // valid in thread 0
+}
+
+__device__ __forceinline__ float bits_from_prob(float p) {
+  const float b = -1.0f * logf(p + 1e-5f) / 0.69314718055994530942f;
+  return fmaxf(b, 0.f);
+}
+
+__device__ __forceinline__ float laplace_cdf(float x, float scale) {
+  const float sg = (x > 0.f) ? 1.f : ((x < 0.f) ? -1.f : 0.f);
+  return 0.5f - 0.5f * sg * expm1f(-fabsf(x) / scale);
+}
+__device__ __forceinline__ float normal_cdf(float x, float scale) {
+  return 0.5f * (1.f + erff(x * (1.f / scale) / 1.41421356237309504880f));
+}
+
+__global__ void __launch_bounds__(256)
+latent_bits_kernel(const float* __restrict__ yq, const float* __restrict__ sc, float* __restrict__ partial,
+                   int64_t per_sample, int nblk, int dist) {
+  const int n = blockIdx.y, b = blockIdx.x;
+  const int64_t i0 = (int64_t)b * RED_CHUNK;
+  const int64_t i1 = i0 + RED_CHUNK < per_sample ? i0 + RED_CHUNK : per_sample;
+  float acc = 0.f;
+  for (int64_t i = i0 + threadIdx.x; i < i1; i += 256) {
+    const float v = yq[(int64_t)n * per_sample + i];
+    float s = sc[(int64_t)n * per_sample + i];
+    float p;
+    if (dist == 0) {
+      s = fminf(fmaxf(s, 1e-5f), 1e10f);
+      p = laplace_cdf(v + 0.5f, s) - laplace_cdf(v - 0.5f, s);
+    } else {
+      s = fminf(fmaxf(s, 0.11f), 1e10f);
+      p = normal_cdf(v + 0.5f, s) - normal_cdf(v - 0.5f, s);
+    }
+    acc += bits_from_prob(p);
+  }
+  const float t = block_sum_256(acc);
+  if (threadIdx.x == 0) partial[(int64_t)n * nblk + b] = t;
+}
+
+__device__ __forceinline__ float softplus_f(float x) { return x > 20.f ? x : log1pf(expf(x)); }
+
+__device__ __forceinline__ float factorized_cdf(float x, const float* __restrict__ fp, int C, int c) {
+  // fp rows: f1.h f1.b f1.a f2.h f2.b f2.a f3.h f3.b f3.a f4.h f4.b
+#pragma unroll
+  for (int l = 0; l < 3; ++l) {
+    x = x * softplus_f(__ldg(fp + (3 * l) * C + c)) + __ldg(fp + (3 * l + 1) * C + c);
+    x = x + tanhf(x) * tanhf(__ldg(fp + (3 * l + 2) * C + c));
+  }
+  x = x * softplus_f(__ldg(fp + 9 * C + c)) + __ldg(fp + 10 * C + c);
+  return 1.f / (1.f + expf(-x));
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256)
+factorized_bits_kernel(const T* __restrict__ z, const float* __restrict__ fp, float* __restrict__ partial,
+                       int64_t hw, int C, int cs, int nblk) {
+  const int n = blockIdx.y, b = blockIdx.x;
+  const int64_t per_sample = hw * C;
+  const int64_t i0 = (int64_t)b * RED_CHUNK;
+  const int64_t i1 = i0 + RED_CHUNK < per_sample ? i0 + RED_CHUNK : per_sample;
+  float acc = 0.f;
+  for (int64_t i = i0 + threadIdx.x; i < i1; i += 256) {
+    const int64_t p = i / C;
+    const int c = (int)(i - p * C);
+    const float v = ld_as_float(z + ((int64_t)n * hw + p) * cs + c);
+    const float pr = factorized_cdf(v + 0.5f, fp, C, c) - factorized_cdf(v - 0.5f, fp, C, c);
+    acc += bits_from_prob(pr);
+  }
+  const float t = block_sum_256(acc);
+  if (threadIdx.x == 0) partial[(int64_t)n * nblk + b] = t;
+}
+
+__global__ void __launch_bounds__(256)
+sq_err_kernel(const float* __restrict__ a, const float* __restrict__ bb, float* __restrict__ partial,
+              int64_t per_sample, int nblk) {
+  const int n = blockIdx.y, b = blockIdx.x;
+  const int64_t i0 = (int64_t)b * RED_CHUNK;
+  const int64_t i1 = i0 + RED_CHUNK < per_sample ? i0 + RED_CHUNK : per_sample;
+  float acc = 0.f;
+  for (int64_t i = i0 + threadIdx.x; i < i1; i += 256) {
+    const float d = a[(int64_t)n * per_sample + i] - bb[(int64_t)n * per_sample + i];
+    acc = fmaf(d, d, acc);
+  }
+  const float t = block_sum_256(acc);
+  if (threadIdx.x == 0) partial[(int64_t)n * nblk + b] = t;
+}
+
+__global__ void final_sum_kernel(const float* __restrict__ partial, float* __restrict__ out, int nblk) {
+  // one warp per sample; lane-strided double accumulation in a fixed order
+  const int n = blockIdx.x;
+  double acc = 0.0;
+  for (int b = threadIdx.x; b < nblk; b += 32) acc += (double)partial[(int64_t)n * nblk + b];
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+  if (threadIdx.x == 0) out[n] = (float)acc;
+}
+
+int check_dp(const vcm_dp_desc* d) {
+  if (!d) return 1;
+  if (d->N <= 0 || d->h <= 0 || d->w <= 0 || d->C <= 0 || (d->C & 1)) return 1;
+  if (d->mode < 0 || d->mode > 2) return 1;
+  return 0;
+}
+
+}  // namespace
+
+extern "C" int vcm_dual_prior_pass0(const vcm_dp_desc* d, const void* y, const void* fusion,
+                                    void* params, float* yq, int16_t* sym, uint8_t* idx,
+                                    float* y_q_full, float* scales_full, void* stream) {
+  VCM_CHECK_ARG(check_dp(d) == 0, "bad descriptor");
+  VCM_CHECK_ARG(fusion && params, "null tensor");
+  VCM_CHECK_ARG(d->mode != 0 || (y && yq && sym && idx), "encode mode needs y, yq, sym, idx");
+  VCM_CHECK_ARG(d->mode != 1 || idx, "index mode needs idx");
+  VCM_CHECK_ARG(d->mode != 2 || sym, "reconstruct mode needs sym");
+  VCM_CHECK_ARG((y_q_full == nullptr) == (scales_full == nullptr), "y_q_full/scales_full go together");
+  const int64_t total = (int64_t)d->N * (d->C / 2) * d->h * d->w;
+  VCM_DISPATCH_DTYPE(d->dtype, (dual_prior_pass0_kernel<T><<<ew_grid(total), 256, 0, (cudaStream_t)stream>>>(
+                                   *d, (const T*)y, (const T*)fusion, (T*)params, yq, sym, idx, y_q_full,
+                                   scales_full)));
+  VCM_CHECK_LAUNCH();
+  return 0;
+}
+
+extern "C" int vcm_dual_prior_pass1(const vcm_dp_desc* d, const float* yq, const void* fusion,
+                                    const void* prior, const void* params, const float* q_outer,
+                                    void* y_hat, int16_t* sym, uint8_t* idx, float* y_q_full,
+                                    float* scales_full, void* stream) {
+  (void)fusion;
+  VCM_CHECK_ARG(check_dp(d) == 0, "bad descriptor");
+  VCM_CHECK_ARG(prior && params, "null tensor");
+  VCM_CHECK_ARG(d->mode != 0 || (yq && sym && idx && y_hat && q_outer), "encode mode needs yq, sym, idx, y_hat");
+  VCM_CHECK_ARG(d->mode != 1 || idx, "index mode needs idx");
+  VCM_CHECK_ARG(d->mode != 2 || (sym && y_hat && q_outer), "reconstruct mode needs sym, y_hat");
+  VCM_CHECK_ARG((y_q_full == nullptr) == (scales_full == nullptr), "y_q_full/scales_full go together");
+  const int64_t total = (int64_t)d->N * (d->C / 2) * d->h * d->w;
+  VCM_DISPATCH_DTYPE(d->dtype, (dual_prior_pass1_kernel<T><<<ew_grid(total), 256, 0, (cudaStream_t)stream>>>(
+                                   *d, yq, (const T*)prior, (const T*)params, q_outer, (T*)y_hat, sym, idx,
+                                   y_q_full, scales_full)));
+  VCM_CHECK_LAUNCH();
+  return 0;
+}
+
+extern "C" int vcm_round_latent(const void* z, void* z_hat, int16_t* sym, int32_t N, int32_t h,
+                                int32_t w, int32_t C, int32_t z_cstride, int32_t zhat_cstride,
+                                int32_t dtype, void* stream) {
+  VCM_CHECK_ARG(z && z_hat && N > 0 && h > 0 && w > 0 && C > 0, "bad argument");
+  const int64_t total = (int64_t)N * C * h * w;
+  VCM_DISPATCH_DTYPE(dtype, (round_latent_kernel<T><<<ew_grid(total), 256, 0, (cudaStream_t)stream>>>(
+                                (const T*)z, (T*)z_hat, sym, N, h, w, C, z_cstride, zhat_cstride)));
+  VCM_CHECK_LAUNCH();
+  return 0;
+}
+
+extern "C" int vcm_symbols_to_latent(const int16_t* sym, void* z_hat, int32_t N, int32_t h, int32_t w,
+                                     int32_t C, int32_t zhat_cstride, int32_t dtype, void* stream) {
+  VCM_CHECK_ARG(sym && z_hat && N > 0 && h > 0 && w > 0 && C > 0, "bad argument");
+  const int64_t total = (int64_t)N * C * h * w;
+  VCM_DISPATCH_DTYPE(dtype, (symbols_to_latent_kernel<T><<<ew_grid(total), 256, 0, (cudaStream_t)stream>>>(
+                                sym, (T*)z_hat, N, h, w, C, zhat_cstride)));
+  VCM_CHECK_LAUNCH();
+  return 0;
+}
+
+extern "C" int32_t vcm_bits_partial_count(int64_t per_sample) { return cdiv(per_sample, RED_CHUNK); }
+
+extern "C" int vcm_latent_bits(const float* y_q, const float* scales, float* partial, float* out_bits,
+                               int32_t N, int64_t per_sample, int32_t dist, void* stream) {
+  VCM_CHECK_ARG(y_q && scales && partial && out_bits && N > 0 && per_sample > 0, "bad argument");
+  VCM_CHECK_ARG(dist == 0 || dist == 1, "dist must be 0 (laplace) or 1 (normal)");
+  const int nblk = cdiv(per_sample, RED_CHUNK);
+  cudaStream_t s = (cudaStream_t)stream;
+  latent_bits_kernel<<<dim3(nblk, N), 256, 0, s>>>(y_q, scales, partial, per_sample, nblk, dist);
+  VCM_CHECK_LAUNCH();
+  final_sum_kernel<<<N, 32, 0, s>>>(partial, out_bits, nblk);
+  VCM_CHECK_LAUNCH();
+  return 0;
+}
+
+extern "C" int vcm_factorized_bits(const void* z_hat, const float* fparams, float* partial,
+                                   float* out_bits, int32_t N, int64_t hw, int32_t C, int32_t cstride,
+                                   int32_t dtype, void* stream) {
+  VCM_CHECK_ARG(z_hat && fparams && partial && out_bits && N > 0 && hw > 0 && C > 0, "bad argument");
+  const int nblk = cdiv(hw * C, RED_CHUNK);
+  cudaStream_t s = (cudaStream_t)stream;
+  VCM_DISPATCH_DTYPE(dtype, (factorized_bits_kernel<T><<<dim3(nblk, N), 256, 0, s>>>(
+                                (const T*)z_hat, fparams, partial, hw, C, cstride, nblk)));
+  VCM_CHECK_LAUNCH();
+  final_sum_kernel<<<N, 32, 0, s>>>(partial, out_bits, nblk);
+  VCM_CHECK_LAUNCH();
+  return 0;
+}
+
+extern "C" int vcm_sq_err_sum(const float* a, const float* b, float* partial, float* out, int32_t N,
+                              int64_t per_sample, void* stream) {
+  VCM_CHECK_ARG(a && b && partial && out && N > 0 && per_sample > 0, "bad argument");
+  const int nblk = cdiv(per_sample, RED_CHUNK);
+  cudaStream_t s = (cudaStream_t)stream;
+  sq_err_kernel<<<dim3(nblk, N), 256, 0, s>>>(a, b, partial, per_sample, nblk);
+  VCM_CHECK_LAUNCH();
+  final_sum_kernel<<<N, 32, 0, s>>>(partial, out, nblk);
+  VCM_CHECK_LAUNCH();
+  return 0;
+}

@@ -1,0 +1,235 @@
+// vcm_ts_b200/csrc/layout.cu -- HBM-bound glue kernels: NCHW<->NHWC, channel-slice copy,
+// per-channel scale, 2x2 max-pool, SELayer (deterministic mean + FC + sigmoid).
+// Reference: video_net.py:149-162 (SELayer), :185,207,210 (max_pool2d),
+// video_model.py:280,297,306,326 (per-channel q scaling), video_coder.py:99-117 (NCHW frames).
+#include "common.cuh"
+
+namespace {
+
+// NCHW fp32 -> NHWC: a 32(pixels) x 32(channels) tile is transposed through shared memory so
+// both the read (along W) and the write (along C) are coalesced.
+template <typename T>
+__global__ void nchw_to_nhwc_kernel(const float* __restrict__ src, T* __restrict__ dst, int C,
+                                    int64_t HW, int dst_cs) {
+  __shared__ float tile[32][33];
+  const int n = blockIdx.z;
+  const int64_t p0 = (int64_t)blockIdx.x * 32;
+  const int c0 = blockIdx.y * 32;
+  const int tx = threadIdx.x, ty = threadIdx.y;  // 32 x 8
+  for (int j = ty; j < 32; j += 8) {
+    const int c = c0 + j;
+    const int64_t p = p0 + tx;
+    tile[j][tx] = (c < C && p < HW) ? __ldg(src + ((int64_t)n * C + c) * HW + p) : 0.f;
+  }
+  __syncthreads();
+  for (int j = ty; j < 32; j += 8) {
+    const int64_t p = p0 + j;
+    const int c = c0 + tx;
+    if (c < C && p < HW) st_from_float(dst + ((int64_t)n * HW + p) * dst_cs + c, tile[tx][j]);
+  }
+}
+
+template <typename T>
+__global__ void nhwc_to_nchw_kernel(const T* __restrict__ src, float* __restrict__ dst, int C,
+                                    int64_t HW, int src_cs, int do_clamp, float lo, float hi) {
+  __shared__ float tile[32][33];
+  const int n = blockIdx.z;
+  const int64_t p0 = (int64_t)blockIdx.x * 32;
+  const int c0 = blockIdx.y * 32;
+  const int tx = threadIdx.x, ty = threadIdx.y;
+  for (int j = ty; j < 32; j += 8) {
+    const int64_t p = p0 + j;
+    const int c = c0 + tx;
+    tile[j][tx] = (c < C && p < HW) ? ld_as_float(src + ((int64_t)n * HW + p) * src_cs + c) : 0.f;
+  }
+  __syncthreads();
+  for (int j = ty; j < 32; j += 8) {
+    const int c = c0 + j;
+    const int64_t p = p0 + tx;
+    if (c < C && p < HW) {
+      float v = tile[tx][j];
+      if (do_clamp) v = fminf(fmaxf(v, lo), hi);
+      dst[((int64_t)n * C + c) * HW + p] = v;
+    }
+  }
+}
+
+template <typename T>
+__global__ void copy_channels_kernel(const T* __restrict__ src, T* __restrict__ dst, int64_t npix,
+                                     int C, int src_cs, int dst_cs) {
+  const int64_t total = npix * C;
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total;
+       i += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t p = i / C;
+    const int c = (int)(i - p * C);
+    dst[p * dst_cs + c] = src[p * src_cs + c];
+  }
+}
+
+template <typename T>
+__global__ void scale_channels_kernel(const T* __restrict__ src, T* __restrict__ dst,
+                                      const float* __restrict__ vec, int64_t hw, int C, int src_cs,
+                                      int dst_cs, int op, int64_t total) {
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total;
+       i += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t p = i / C;
+    const int c = (int)(i - p * C);
+    const int n = (int)(p / hw);
+    const float v = ld_as_float(src + p * src_cs + c);
+    const float s = __ldg(vec + (int64_t)n * C + c);
+    st_from_float(dst + p * dst_cs + c, op == 0 ? __fdiv_rn(v, s) : __fmul_rn(v, s));
+  }
+}
+
+template <typename T>
+__global__ void maxpool2_kernel(const T* __restrict__ src, T* __restrict__ dst, int N, int H, int W,
+                                int C, int src_cs, int dst_cs) {
+  const int Ho = H / 2, Wo = W / 2;
+  const int64_t total = (int64_t)N * Ho * Wo * C;
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total;
+       i += (int64_t)gridDim.x * blockDim.x) {
+    const int c = (int)(i % C);
+    int64_t p = i / C;
+    const int ox = (int)(p % Wo);
+    p /= Wo;
+    const int oy = (int)(p % Ho);
+    const int n = (int)(p / Ho);
+    const T* s = src + (((int64_t)n * H + 2 * oy) * W + 2 * ox) * src_cs + c;
+    const float a = ld_as_float(s), b = ld_as_float(s + src_cs);
+    const float e = ld_as_float(s + (int64_t)W * src_cs), f = ld_as_float(s + (int64_t)(W + 1) * src_cs);
+    st_from_float(dst + (((int64_t)n * Ho + oy) * Wo + ox) * dst_cs + c, fmaxf(fmaxf(a, b), fmaxf(e, f)));
+  }
+}
+
+// ---- SELayer -------------------------------------------------------------------------------
+// stage 1: block b of sample n sums a fixed pixel range for every channel (fixed order ->
+// deterministic); stage 2: one block per sample adds the partials in index order, divides by
+// H*W, and applies the two bias-free Linear layers.
+constexpr int SE_PIX_PER_BLOCK = 4096;
+
+template <typename T>
+__global__ void se_partial_kernel(const T* __restrict__ x, float* __restrict__ partial, int64_t hw,
+                                  int C, int cs, int nblk) {
+  extern __shared__ float sm[];  // [rows][C]
+  const int n = blockIdx.y, b = blockIdx.x;
+  const int rows = blockDim.x / C;  // pixel lanes per step (blockDim multiple of C, C <= 256)
+  const int c = threadIdx.x % C, r = threadIdx.x / C;
+  const int64_t p0 = (int64_t)b * SE_PIX_PER_BLOCK;
+  const int64_t p1 = (p0 + SE_PIX_PER_BLOCK < hw) ? p0 + SE_PIX_PER_BLOCK : hw;
+  float s = 0.f;
+  if (r < rows)
+    for (int64_t p = p0 + r; p < p1; p += rows) s += ld_as_float(x + ((int64_t)n * hw + p) * cs + c);
+  if (r < rows) sm[r * C + c] = s;
+  __syncthreads();
+  if (r == 0) {
+    float tot = 0.f;
+    for (int k = 0; k < rows; ++k) tot += sm[k * C + c];
+    partial[((int64_t)n * nblk + b) * C + c] = tot;
+  }
+}
+
+__global__ void se_fc_kernel(const float* __restrict__ partial, const float* __restrict__ w1,
+                             const float* __restrict__ w2, float* __restrict__ scale, int64_t hw,
+                             int C, int Cmid, int nblk) {
+  extern __shared__ float sm[];  // mean[C] + hid[Cmid]
+  float* mean = sm;
+  float* hid = sm + C;
+  const int n = blockIdx.x;
+  for (int c = threadIdx.x; c < C; c += blockDim.x) {
+    float s = 0.f;
+    for (int b = 0; b < nblk; ++b) s += partial[((int64_t)n * nblk + b) * C + c];
+    mean[c] = s / (float)hw;
+  }
+  __syncthreads();
+  for (int j = threadIdx.x; j < Cmid; j += blockDim.x) {
+    float s = 0.f;
+    for (int c = 0; c < C; ++c) s = fmaf(mean[c], w1[j * C + c], s);
+    hid[j] = fmaxf(s, 0.f);
+  }
+  __syncthreads();
+  for (int c = threadIdx.x; c < C; c += blockDim.x) {
+    float s = 0.f;
+    for (int j = 0; j < Cmid; ++j) s = fmaf(hid[j], w2[c * Cmid + j], s);
+    scale[(int64_t)n * C + c] = 1.f / (1.f + expf(-s));
+  }
+}
+
+inline int ew_grid(int64_t total) {
+  int64_t g = (total + 255) / 256;
+  return (int)(g > 148 * 16 ? 148 * 16 : (g < 1 ? 1 : g));
+}
+
+}  // namespace
+
+extern "C" int vcm_nchw_to_nhwc(const float* src, void* dst, int32_t N, int32_t C, int32_t H,
+                                int32_t W, int32_t dst_cstride, int32_t dtype, void* stream) {
+  VCM_CHECK_ARG(src && dst && N > 0 && C > 0 && H > 0 && W > 0 && dst_cstride >= C, "bad argument");
+  const int64_t HW = (int64_t)H * W;
+  dim3 grid(cdiv(HW, 32), cdiv(C, 32), N), block(32, 8);
+  VCM_DISPATCH_DTYPE(dtype, (nchw_to_nhwc_kernel<T><<<grid, block, 0, (cudaStream_t)stream>>>(
+                                src, (T*)dst, C, HW, dst_cstride)));
+  VCM_CHECK_LAUNCH();
+  return 0;
+}
+
+extern "C" int vcm_nhwc_to_nchw(const void* src, float* dst, int32_t N, int32_t C, int32_t H,
+                                int32_t W, int32_t src_cstride, int32_t dtype, int32_t do_clamp,
+                                float lo, float hi, void* stream) {
+  VCM_CHECK_ARG(src && dst && N > 0 && C > 0 && H > 0 && W > 0 && src_cstride >= C, "bad argument");
+  const int64_t HW = (int64_t)H * W;
+  dim3 grid(cdiv(HW, 32), cdiv(C, 32), N), block(32, 8);
+  VCM_DISPATCH_DTYPE(dtype, (nhwc_to_nchw_kernel<T><<<grid, block, 0, (cudaStream_t)stream>>>(
+                                (const T*)src, dst, C, HW, src_cstride, do_clamp, lo, hi)));
+  VCM_CHECK_LAUNCH();
+  return 0;
+}
+
+extern "C" int vcm_copy_channels(const void* src, void* dst, int64_t npix, int32_t C,
+                                 int32_t src_cstride, int32_t dst_cstride, int32_t dtype,
+                                 void* stream) {
+  VCM_CHECK_ARG(src && dst && npix > 0 && C > 0, "bad argument");
+  VCM_DISPATCH_DTYPE(dtype, (copy_channels_kernel<T><<<ew_grid(npix * C), 256, 0, (cudaStream_t)stream>>>(
+                                (const T*)src, (T*)dst, npix, C, src_cstride, dst_cstride)));
+  VCM_CHECK_LAUNCH();
+  return 0;
+}
+
+extern "C" int vcm_scale_channels(const void* src, void* dst, const float* vec, int32_t N, int64_t hw,
+                                  int32_t C, int32_t src_cstride, int32_t dst_cstride, int32_t op,
+                                  int32_t dtype, void* stream) {
+  VCM_CHECK_ARG(src && dst && vec && N > 0 && hw > 0 && C > 0 && (op == 0 || op == 1), "bad argument");
+  const int64_t total = (int64_t)N * hw * C;
+  VCM_DISPATCH_DTYPE(dtype, (scale_channels_kernel<T><<<ew_grid(total), 256, 0, (cudaStream_t)stream>>>(
+                                (const T*)src, (T*)dst, vec, hw, C, src_cstride, dst_cstride, op, total)));
+  VCM_CHECK_LAUNCH();
+  return 0;
+}
+
+extern "C" int vcm_maxpool2(const void* src, void* dst, int32_t N, int32_t H, int32_t W, int32_t C,
+                            int32_t src_cstride, int32_t dst_cstride, int32_t dtype, void* stream) {
+  VCM_CHECK_ARG(src && dst && N > 0 && H > 1 && W > 1 && C > 0, "bad argument");
+  const int64_t total = (int64_t)N * (H / 2) * (W / 2) * C;
+  VCM_DISPATCH_DTYPE(dtype, (maxpool2_kernel<T><<<ew_grid(total), 256, 0, (cudaStream_t)stream>>>(
+                                (const T*)src, (T*)dst, N, H, W, C, src_cstride, dst_cstride)));
+  VCM_CHECK_LAUNCH();
+  return 0;
+}
+
+extern "C" int32_t vcm_se_partial_count(int64_t hw) { return cdiv(hw, SE_PIX_PER_BLOCK); }
+
+extern "C" int vcm_se_scale(const void* x, float* partial, const float* w1, const float* w2,
+                            float* scale, int32_t N, int64_t hw, int32_t C, int32_t Cmid,
+                            int32_t cstride, int32_t dtype, void* stream) {
+  VCM_CHECK_ARG(x && partial && w1 && w2 && scale && N > 0 && hw > 0, "bad argument");
+  VCM_CHECK_ARG(C > 0 && C <= 256 && Cmid > 0 && Cmid <= 64, "SELayer channels out of range");
+  const int nblk = cdiv(hw, SE_PIX_PER_BLOCK);
+  const int rows = 512 / C >= 1 ? 512 / C : 1;
+  const int threads = rows * C;
+  cudaStream_t s = (cudaStream_t)stream;
+  VCM_DISPATCH_DTYPE(dtype, (se_partial_kernel<T><<<dim3(nblk, N), threads, threads * sizeof(float), s>>>(
+                                (const T*)x, partial, hw, C, cstride, nblk)));
+  VCM_CHECK_LAUNCH();
+  se_fc_kernel<<<N, 256, (C + Cmid) * sizeof(float), s>>>(partial, w1, w2, scale, hw, C, Cmid, nblk);
+  VCM_CHECK_LAUNCH();
+  return 0;
+}

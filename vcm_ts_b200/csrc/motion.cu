@@ -1,0 +1,232 @@
+// vcm_ts_b200/csrc/motion.cu -- motion glue: SpyNet pyramid pooling, flow x2 up / half down,
+// and the bilinear backward warp.  All HBM-bound gather/stream kernels over NHWC views.
+//
+//   vcm_avgpool2    F.avg_pool2d(x, 2, 2)                        video_net.py:131-133
+//   vcm_flow_up2    bilinearupsacling(flow) * gain               video_net.py:58-63, :140
+//   vcm_flow_down2  bilineardownsacling(mv) * gain (gain = 1/2)  video_net.py:66-71, video_model.py:237-238
+//   vcm_flow_warp   torch_warp: grid_sample(bilinear, border, align_corners=True) at
+//                   linspace(-1,1) + flow/((size-1)/2)           video_net.py:32-55
+//
+// The warp restates ATen's fp32 arithmetic step by step (normalise -> unnormalise -> clip ->
+// floor -> 4 taps) instead of the algebraically equal x + u, so border clipping and sub-pixel
+// weights round the way the reference's do.
+#include "common.cuh"
+
+namespace {
+
+inline int ew_grid(int64_t total) {
+  int64_t g = (total + 255) / 256;
+  return (int)(g > 148 * 16 ? 148 * 16 : (g < 1 ? 1 : g));
+}
+
+__global__ void avgpool2_kernel(const float* __restrict__ src, float* __restrict__ dst, int N, int H,
+                                int W, int C, int src_cs, int dst_cs) {
+  const int Ho = H / 2, Wo = W / 2;
+  const int64_t total = (int64_t)N * Ho * Wo * C;
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total;
+       i += (int64_t)gridDim.x * blockDim.x) {
+    const int c = (int)(i % C);
+    int64_t p = i / C;
+    const int ox = (int)(p % Wo);
+    p /= Wo;
+    const int oy = (int)(p % Ho);
+    const int n = (int)(p / Ho);
+    const float* s = src + (((int64_t)n * H + 2 * oy) * W + 2 * ox) * src_cs + c;
+    float v = __ldg(s);
+    v = __fadd_rn(v, __ldg(s + src_cs));
+    v = __fadd_rn(v, __ldg(s + (int64_t)W * src_cs));
+    v = __fadd_rn(v, __ldg(s + (int64_t)(W + 1) * src_cs));
+    dst[(((int64_t)n * Ho + oy) * Wo + ox) * dst_cs + c] = __fdiv_rn(v, 4.f);
+  }
+}
+
+// align_corners=False x2 upsample of a 2-channel field: src index = d/2 - 0.25 clamped at 0
+__global__ void flow_up2_kernel(const float* __restrict__ src, float* __restrict__ dst, int N, int H,
+                                int W, int src_cs, int dst_cs, float gain) {
+  const int Ho = 2 * H, Wo = 2 * W;
+  const int64_t total = (int64_t)N * Ho * Wo;
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total;
+       i += (int64_t)gridDim.x * blockDim.x) {
+    const int ox = (int)(i % Wo);
+    int64_t p = i / Wo;
+    const int oy = (int)(p % Ho);
+    const int n = (int)(p / Ho);
+    float sy = fmaxf((oy + 0.5f) * 0.5f - 0.5f, 0.f);
+    float sx = fmaxf((ox + 0.5f) * 0.5f - 0.5f, 0.f);
+    const int y0 = (int)sy, x0 = (int)sx;
+    const int y1 = y0 + (y0 < H - 1 ? 1 : 0), x1 = x0 + (x0 < W - 1 ? 1 : 0);
+    const float ly = sy - y0, lx = sx - x0;
+    const float hy = 1.f - ly, hx = 1.f - lx;
+    const float* b = src + (int64_t)n * H * W * src_cs;
+#pragma unroll
+    for (int c = 0; c < 2; ++c) {
+      const float p00 = __ldg(b + ((int64_t)y0 * W + x0) * src_cs + c);
+      const float p01 = __ldg(b + ((int64_t)y0 * W + x1) * src_cs + c);
+      const float p10 = __ldg(b + ((int64_t)y1 * W + x0) * src_cs + c);
+      const float p11 = __ldg(b + ((int64_t)y1 * W + x1) * src_cs + c);
+      const float top = __fadd_rn(__fmul_rn(hx, p00), __fmul_rn(lx, p01));
+      const float bot = __fadd_rn(__fmul_rn(hx, p10), __fmul_rn(lx, p11));
+      const float v = __fadd_rn(__fmul_rn(hy, top), __fmul_rn(ly, bot));
+      dst[i * dst_cs + c] = __fmul_rn(v, gain);
+    }
+  }
+}
+
+// align_corners=False half-size bilinear of an even-sized field == 2x2 mean, then * gain
+__global__ void flow_down2_kernel(const float* __restrict__ src, float* __restrict__ dst, int N,
+                                  int H, int W, int src_cs, int dst_cs, float gain) {
+  const int Ho = H / 2, Wo = W / 2;
+  const int64_t total = (int64_t)N * Ho * Wo;
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total;
+       i += (int64_t)gridDim.x * blockDim.x) {
+    const int ox = (int)(i % Wo);
+    int64_t p = i / Wo;
+    const int oy = (int)(p % Ho);
+    const int n = (int)(p / Ho);
+    const float* s = src + (((int64_t)n * H + 2 * oy) * W + 2 * ox) * src_cs;
+#pragma unroll
+    for (int c = 0; c < 2; ++c) {
+      const float p00 = __ldg(s + c), p01 = __ldg(s + src_cs + c);
+      const float p10 = __ldg(s + (int64_t)W * src_cs + c), p11 = __ldg(s + (int64_t)(W + 1) * src_cs + c);
+      const float top = __fadd_rn(__fmul_rn(0.5f, p00), __fmul_rn(0.5f, p01));
+      const float bot = __fadd_rn(__fmul_rn(0.5f, p10), __fmul_rn(0.5f, p11));
+      const float v = __fadd_rn(__fmul_rn(0.5f, top), __fmul_rn(0.5f, bot));
+      dst[i * dst_cs + c] = __fmul_rn(v, gain);
+    }
+  }
+}
+
+// torch.linspace(-1, 1, steps)[i] in fp32 (two-sided evaluation, RangeFactories.cpp)
+__device__ __forceinline__ float linspace_pm1(int i, int steps) {
+  const float step = __fdiv_rn(2.f, (float)(steps - 1));
+  return (i < steps / 2) ? __fadd_rn(-1.f, __fmul_rn(step, (float)i))
+                         : __fsub_rn(1.f, __fmul_rn(step, (float)(steps - 1 - i)));
+}
+
+struct WarpTaps {
+  int x0, x1, y0, y1;
+  float nw, ne, sw, se;
+  bool x1_ok, y1_ok;
+};
+
+__device__ __forceinline__ WarpTaps warp_taps(float u, float v, int ox, int oy, int W, int H) {
+  const float sxf = __fdiv_rn((float)W - 1.f, 2.f), syf = __fdiv_rn((float)H - 1.f, 2.f);
+  const float gx = __fadd_rn(linspace_pm1(ox, W), __fdiv_rn(u, sxf));
+  const float gy = __fadd_rn(linspace_pm1(oy, H), __fdiv_rn(v, syf));
+  float x = __fmul_rn(__fadd_rn(gx, 1.f), sxf);
+  float y = __fmul_rn(__fadd_rn(gy, 1.f), syf);
+  x = fminf((float)(W - 1), fmaxf(x, 0.f));
+  y = fminf((float)(H - 1), fmaxf(y, 0.f));
+  const float xw = floorf(x), yn = floorf(y);
+  const float w = __fsub_rn(x, xw), e = __fsub_rn(1.f, w);
+  const float nn = __fsub_rn(y, yn), s = __fsub_rn(1.f, nn);
+  WarpTaps t;
+  t.x0 = (int)xw; t.y0 = (int)yn;
+  t.x1 = t.x0 + 1; t.y1 = t.y0 + 1;
+  t.x1_ok = t.x1 <= W - 1; t.y1_ok = t.y1 <= H - 1;
+  if (!t.x1_ok) t.x1 = W - 1;
+  if (!t.y1_ok) t.y1 = H - 1;
+  t.nw = __fmul_rn(s, e); t.ne = __fmul_rn(s, w);
+  t.sw = __fmul_rn(nn, e); t.se = __fmul_rn(nn, w);
+  return t;
+}
+
+__device__ __forceinline__ float warp_mix(const WarpTaps& t, float a, float b, float c, float d) {
+  // out-of-range east / south taps contribute exactly 0 (masked gather in ATen)
+  const float t0 = __fmul_rn(a, t.nw);
+  const float t1 = t.x1_ok ? __fmul_rn(b, t.ne) : 0.f;
+  const float t2 = t.y1_ok ? __fmul_rn(c, t.sw) : 0.f;
+  const float t3 = (t.x1_ok && t.y1_ok) ? __fmul_rn(d, t.se) : 0.f;
+  return __fadd_rn(__fadd_rn(__fadd_rn(t0, t1), t2), t3);
+}
+
+// one thread = one pixel x 4 channels (VEC) or x 1 channel
+template <typename T, bool VEC>
+__global__ void flow_warp_kernel(const T* __restrict__ feat, const float* __restrict__ flow,
+                                 T* __restrict__ out, int N, int H, int W, int C, int feat_cs,
+                                 int flow_cs, int out_cs) {
+  const int G = VEC ? C / 4 : C;
+  const int64_t total = (int64_t)N * H * W * G;
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total;
+       i += (int64_t)gridDim.x * blockDim.x) {
+    const int g = (int)(i % G);
+    const int64_t p = i / G;
+    const int ox = (int)(p % W);
+    const int64_t q = p / W;
+    const int oy = (int)(q % H);
+    const int n = (int)(q / H);
+    const float2 uv = make_float2(__ldg(flow + p * flow_cs), __ldg(flow + p * flow_cs + 1));
+    const WarpTaps t = warp_taps(uv.x, uv.y, ox, oy, W, H);
+    const T* b = feat + (int64_t)n * H * W * feat_cs;
+    const int c = VEC ? g * 4 : g;
+    const T* p00 = b + ((int64_t)t.y0 * W + t.x0) * feat_cs + c;
+    const T* p01 = b + ((int64_t)t.y0 * W + t.x1) * feat_cs + c;
+    const T* p10 = b + ((int64_t)t.y1 * W + t.x0) * feat_cs + c;
+    const T* p11 = b + ((int64_t)t.y1 * W + t.x1) * feat_cs + c;
+    if (VEC) {
+      const float4 a = ld4<T>(p00), bb = ld4<T>(p01), cc = ld4<T>(p10), dd = ld4<T>(p11);
+      float4 r;
+      r.x = warp_mix(t, a.x, bb.x, cc.x, dd.x);
+      r.y = warp_mix(t, a.y, bb.y, cc.y, dd.y);
+      r.z = warp_mix(t, a.z, bb.z, cc.z, dd.z);
+      r.w = warp_mix(t, a.w, bb.w, cc.w, dd.w);
+      st4<T>(out + p * out_cs + c, r);
+    } else {
+      st_from_float(out + p * out_cs + c,
+                    warp_mix(t, ld_as_float(p00), ld_as_float(p01), ld_as_float(p10), ld_as_float(p11)));
+    }
+  }
+}
+
+}  // namespace
+
+extern "C" int vcm_avgpool2(const float* src, float* dst, int32_t N, int32_t H, int32_t W, int32_t C,
+                            int32_t src_cstride, int32_t dst_cstride, void* stream) {
+  VCM_CHECK_ARG(src && dst && N > 0 && H > 1 && W > 1 && C > 0, "bad argument");
+  const int64_t total = (int64_t)N * (H / 2) * (W / 2) * C;
+  avgpool2_kernel<<<ew_grid(total), 256, 0, (cudaStream_t)stream>>>(src, dst, N, H, W, C, src_cstride,
+                                                                    dst_cstride);
+  VCM_CHECK_LAUNCH();
+  return 0;
+}
+
+extern "C" int vcm_flow_up2(const float* src, float* dst, int32_t N, int32_t H, int32_t W,
+                            int32_t src_cstride, int32_t dst_cstride, float gain, void* stream) {
+  VCM_CHECK_ARG(src && dst && N > 0 && H > 0 && W > 0, "bad argument");
+  const int64_t total = (int64_t)N * H * W * 4;
+  flow_up2_kernel<<<ew_grid(total), 256, 0, (cudaStream_t)stream>>>(src, dst, N, H, W, src_cstride,
+                                                                    dst_cstride, gain);
+  VCM_CHECK_LAUNCH();
+  return 0;
+}
+
+extern "C" int vcm_flow_down2(const float* src, float* dst, int32_t N, int32_t H, int32_t W,
+                              int32_t src_cstride, int32_t dst_cstride, float gain, void* stream) {
+  VCM_CHECK_ARG(src && dst && N > 0 && H > 1 && W > 1 && H % 2 == 0 && W % 2 == 0, "bad argument");
+  const int64_t total = (int64_t)N * (H / 2) * (W / 2);
+  flow_down2_kernel<<<ew_grid(total), 256, 0, (cudaStream_t)stream>>>(src, dst, N, H, W, src_cstride,
+                                                                      dst_cstride, gain);
+  VCM_CHECK_LAUNCH();
+  return 0;
+}
+
+extern "C" int vcm_flow_warp(const void* feat, const float* flow, void* out, int32_t N, int32_t H,
+                             int32_t W, int32_t C, int32_t feat_cstride, int32_t flow_cstride,
+                             int32_t out_cstride, int32_t dtype, void* stream) {
+  VCM_CHECK_ARG(feat && flow && out && N > 0 && H > 1 && W > 1 && C > 0, "bad argument");
+  const int esz = dtype == VCM_F32 ? 4 : 2;
+  const bool vec = (C % 4 == 0) && (feat_cstride % 4 == 0) && (out_cstride % 4 == 0) &&
+                   ((uintptr_t)feat % (4 * esz) == 0) && ((uintptr_t)out % (4 * esz) == 0);
+  const int64_t total = (int64_t)N * H * W * (vec ? C / 4 : C);
+  cudaStream_t s = (cudaStream_t)stream;
+  VCM_DISPATCH_DTYPE(dtype, {
+    if (vec)
+      flow_warp_kernel<T, true><<<ew_grid(total), 256, 0, s>>>((const T*)feat, flow, (T*)out, N, H, W, C,
+                                                             feat_cstride, flow_cstride, out_cstride);
+    else
+      flow_warp_kernel<T, false><<<ew_grid(total), 256, 0, s>>>((const T*)feat, flow, (T*)out, N, H, W, C,
+                                                              feat_cstride, flow_cstride, out_cstride);
+  });
+  VCM_CHECK_LAUNCH();
+  return 0;
+}

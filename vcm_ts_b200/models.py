@@ -1,0 +1,638 @@
+"""Drop-in `DMC` and `IntraNoAR` modules: the reference's operator API
+(DCVC_HEM/src/models/video_model.py:131-596, image_model.py:16-200, common_model.py:14-217) on top
+of the sm_100a kernels of libvcmts_b200.so.
+
+Same constructor arguments, state-dict keys, method signatures and result dictionaries (including
+the reference's `"dbp"` key in `DMC.compress`), so `video_coder.py`, `benchmark_videos_decoding.py`
+and `DCVC_HEM/test_video.py` can import these classes instead of the reference's.  Callers hand in
+and get back ordinary NCHW fp32 tensors; internally everything is NHWC views (backend.py) and every
+nn.Conv2d / activation / PixelShuffle / concat is a fused device op (nets.py).
+
+`precision` (constructor kwarg or VCM_B200_PRECISION env): "fp32" = exact mode (fp32 FMA convs,
+meant to reproduce the reference's quantised symbols), "bf16" = tcgen05 tensor-core mode.
+There is no CPU path: calling a compute method without a B200 raises.
+"""
+import math
+import os
+import time
+
+import numpy as np
+import torch
+from torch import nn
+
+from . import arch
+from .backend import CudaBackend, View
+from .entropy import CdfTables, RansCoder, ScaleIndexTable, factorized_tables
+from .nets import Graph
+from .stream_helper import (decode_i, decode_p, encode_i, encode_p, filesize, get_downsampled_shape,
+                            get_rounded_q, get_state_dict, pack_i, pack_p, unpack_i, unpack_p)
+
+F32 = torch.float32
+
+
+class _Node(nn.Module):
+    """Anonymous container so parameter names match the reference's module tree."""
+
+
+class _Runtime:
+    """Per-process, per-device state that must not be pickled: backend, packed weights, coder."""
+
+    def __init__(self, backend):
+        self.B = backend
+        self.packed = {}
+        self.lin = {}
+        self.persist = {}
+        self.coder = None
+        self.tables = {}
+
+
+class CompressionModel(nn.Module):
+    """common_model.py:14-49,75-80 twin: parameter tree from a layer table, lazy runtime, update()."""
+
+    def __init__(self, spec, y_distribution, precision=None):
+        super().__init__()
+        self.y_distribution = y_distribution
+        self._precision = precision or os.environ.get("VCM_B200_PRECISION", "fp32")
+        self._rt = None
+        self._backend_factory = None          # tests inject an emulation backend here
+        self.entropy_coder = None             # reference attribute; set by update()
+        self._scale_table = ScaleIndexTable(y_distribution)
+        self._fparam_names = []
+        for kind, name, meta in spec.items:
+            if kind == arch.CONV:
+                cin, cout, k = meta
+                node = self._node(name)
+                w = torch.empty(cout, cin, k, k)
+                nn.init.xavier_normal_(w, math.sqrt(2))          # common_model.py:31-36
+                node.weight = nn.Parameter(w)
+                node.bias = nn.Parameter(torch.full((cout,), 0.01))
+            elif kind == arch.LINEAR:
+                cin, cout = meta
+                node = self._node(name)
+                w = torch.empty(cout, cin)
+                nn.init.kaiming_uniform_(w, a=math.sqrt(5))      # nn.Linear default
+                node.weight = nn.Parameter(w)
+            elif kind == arch.BITPARM:
+                (ch,) = meta
+                self._fparam_names.append(name)
+                for f in ("f1", "f2", "f3", "f4"):
+                    node = self._node(f"{name}.{f}")
+                    node.h = nn.Parameter(torch.nn.init.normal_(torch.empty(1, ch, 1, 1), 0, 0.01))
+                    node.b = nn.Parameter(torch.nn.init.normal_(torch.empty(1, ch, 1, 1), 0, 0.01))
+                    if f != "f4":
+                        node.a = nn.Parameter(torch.nn.init.normal_(torch.empty(1, ch, 1, 1), 0, 0.01))
+            else:
+                self.register_parameter(name, nn.Parameter(torch.ones(meta)))
+
+    def _node(self, dotted):
+        m = self
+        for part in dotted.split("."):
+            if not hasattr(m, part):
+                m.add_module(part, _Node())
+            m = getattr(m, part)
+        return m
+
+    # ---- pickling (benchmark_videos_decoding.py:248-254 pickles modules into a spawn worker)
+    def __getstate__(self):
+        st = dict(self.__dict__)
+        st["_rt"] = None
+        st["_backend_factory"] = None
+        st["entropy_coder"] = None
+        return st
+
+    # ---- runtime ------------------------------------------------------------------------
+    def set_precision(self, precision):
+        if precision != self._precision:
+            self._precision, self._rt = precision, None
+        return self
+
+    @property
+    def device(self):
+        return next(self.parameters()).device
+
+    def _runtime(self):
+        dev = self.device
+        if self._rt is None or self._rt.B.device != dev:
+            if self._backend_factory is not None:
+                backend = self._backend_factory(dev, self._precision)
+            else:
+                backend = CudaBackend(dev, self._precision)      # raises without a B200
+            rt = _Runtime(backend)
+            rt.graph = Graph(backend, lambda n, m=None: self._packed(rt, n, m), lambda n: self._lin(rt, n))
+            self._rt = rt
+        return self._rt
+
+    def _packed(self, rt, name, in_map):
+        w = self.get_parameter(name + ".weight")
+        b = self.get_parameter(name + ".bias")
+        key = (name, tuple(in_map) if in_map is not None else None)
+        tag = (w._version, w.data_ptr(), b._version, b.data_ptr())
+        hit = rt.packed.get(key)
+        if hit is None or hit[0] != tag:
+            hit = (tag, rt.B.pack_conv(w, b, in_map))
+            rt.packed[key] = hit
+        return hit[1]
+
+    def _lin(self, rt, name):
+        w = self.get_parameter(name)
+        tag = (w._version, w.data_ptr())
+        hit = rt.lin.get(name)
+        if hit is None or hit[0] != tag:
+            hit = (tag, w.detach().to(rt.B.device, F32).contiguous())
+            rt.lin[name] = hit
+        return hit[1]
+
+    def _persist(self, rt, key, N, H, W, C, dtype):
+        """Zero-initialised buffer that survives across frames (pad channels stay 0)."""
+        k = (key, N, H, W, C, dtype)
+        v = rt.persist.get(k)
+        if v is None:
+            v = rt.B.new(N, H, W, C, dtype=dtype, zero=True)
+            rt.persist[k] = v
+        return v
+
+    def _fparams(self, rt, name):
+        """[11, C] fp32: f1.h f1.b f1.a f2.h f2.b f2.a f3.h f3.b f3.a f4.h f4.b (vcm_factorized_bits)."""
+        rows = []
+        for f in ("f1", "f2", "f3", "f4"):
+            for p in ("h", "b", "a"):
+                if f == "f4" and p == "a":
+                    continue
+                rows.append(self.get_parameter(f"{name}.{f}.{p}").detach().reshape(-1))
+        return torch.stack(rows).to(rt.B.device, F32).contiguous()
+
+    def _fdict(self, name):
+        out = {}
+        for f in ("f1", "f2", "f3", "f4"):
+            for p in ("h", "b", "a"):
+                if f == "f4" and p == "a":
+                    continue
+                out[f"{f}.{p}"] = self.get_parameter(f"{name}.{f}.{p}")
+        return out
+
+    def update(self, force=False):
+        """common_model.py:75-80: build the CDF tables and the native coder (CPU, once)."""
+        rt = self._runtime()
+        if rt.coder is not None and not force:
+            return
+        rt.coder = RansCoder()
+        self.entropy_coder = rt.coder
+        rt.tables = {"y": CdfTables(*self._scale_table.update())}
+        for name in self._fparam_names:
+            ch = self.get_parameter(name + ".f1.h").shape[1]
+            rt.tables[name] = CdfTables(*factorized_tables(self._fdict(name), ch))
+
+    def _need_coder(self):
+        rt = self._runtime()
+        if rt.coder is None:
+            raise RuntimeError("call update(force=True) before compress/decompress (as in the reference)")
+        return rt
+
+    # ---- q helpers ------------------------------------------------------------------------
+    def _curr_q(self, rt, basic, q_scale, N):
+        """LowerBound(q_basic, .5) * q_scale -> contiguous [N, C] fp32 on the device."""
+        qb = torch.max(basic.detach(), torch.ones_like(basic) * 0.5)
+        if torch.is_tensor(q_scale):
+            q = qb * q_scale.detach().to(qb.device, qb.dtype)
+        else:
+            q = qb * float(q_scale)
+        q = q.reshape(q.shape[0], -1)
+        if q.shape[0] != N:
+            q = q.expand(N, -1)
+        return q.to(rt.B.device, F32).contiguous()
+
+    # ---- host <-> device symbol traffic -----------------------------------------------------
+    @staticmethod
+    def _to_host(*tensors):
+        return [t.cpu() for t in tensors]
+
+    def _decode_plane_fn(self, rt):
+        def decode_plane(idx_dev):
+            idx = idx_dev.cpu()
+            out = torch.empty(idx.shape, dtype=torch.int16)
+            rt.coder.decode_planes(idx, rt.tables["y"], out)
+            return out.to(rt.B.device)
+        return decode_plane
+
+    def _decode_z(self, rt, table_name, C, zs):
+        out = torch.empty((1, C, zs[0], zs[1]), dtype=torch.int16)
+        rt.coder.decode_channels(C, zs[0] * zs[1], rt.tables[table_name], out)
+        return rt.B.symbols_to_latent(out.to(rt.B.device), 1, zs[0], zs[1], C)
+
+
+# ==========================================================================================
+# P-frame model
+# ==========================================================================================
+class DMC(CompressionModel):
+    """video_model.py:131-596."""
+
+    def __init__(self, anchor_num=4, precision=None):
+        super().__init__(arch.dmc_spec(anchor_num), "laplace", precision)
+        self.DMC_version = "1.19"
+        self.channel_mv, self.channel_N, self.channel_M = 64, 64, 96
+        self.anchor_num = int(anchor_num)
+
+    @staticmethod
+    def get_q_scales_from_ckpt(ckpt_path):
+        ckpt = get_state_dict(ckpt_path)
+        return ckpt["y_q_scale"].reshape(-1), ckpt["mv_y_q_scale"].reshape(-1)
+
+    def get_curr_mv_y_q(self, q_scale):
+        return torch.max(self.mv_y_q_basic, torch.ones_like(self.mv_y_q_basic) * 0.5) * q_scale
+
+    def get_curr_y_q(self, q_scale):
+        return torch.max(self.y_q_basic, torch.ones_like(self.y_q_basic) * 0.5) * q_scale
+
+    # ---- shared graph pieces ------------------------------------------------------------------
+    def _ctx_buffer(self, rt, N, H, W):
+        """[feat32 (32) | context1 (64) | x (3) | zero pad] : recon reads [0,96) in the reference's
+        cat order (video_model.py:124,330), the contextual encoder reads [32, 32+Cin_p)."""
+        pad = 13 if rt.B.precision == "bf16" else 1
+        return self._persist(rt, "ctx", N, H, W, 99 + pad, rt.B.act_dtype)
+
+    def _enc_in_map(self, rt):
+        pad = 13 if rt.B.precision == "bf16" else 0
+        # buffer order (context1 0..63, x 64..66, pad) -> reference order cat([x, context1])
+        return [3 + j for j in range(64)] + [0, 1, 2] + [-1] * pad
+
+    def multi_scale_feature_extractor(self, dpb):
+        """video_model.py:226-231, :17-37 -> three NHWC views."""
+        rt = self._runtime()
+        g, B = rt.graph, rt.B
+        if dpb["ref_feature"] is None:
+            f = g.conv("feature_adaptor_I", B.from_nchw(dpb["ref_frame"]))
+        else:
+            f = g.conv("feature_adaptor_P", B.from_nchw(dpb["ref_feature"]))
+        l1 = g.res_block("feature_extractor.res_block1", g.conv("feature_extractor.conv1", f))
+        l2 = g.res_block("feature_extractor.res_block2", g.conv("feature_extractor.conv2", l1, stride=2))
+        l3 = g.res_block("feature_extractor.res_block3", g.conv("feature_extractor.conv3", l2, stride=2))
+        return l1, l2, l3
+
+    def motion_compensation(self, dpb, mv, want_warp_frame=False):
+        """video_model.py:233-246 + MultiScaleContextFusion :40-68.  mv: fp32 flow view.
+        Returns (ctx buffer holding context1 at [32,96), E2 = [f | context2], E3 = [f | context3],
+        warp_frame view or None)."""
+        rt = self._runtime()
+        g, B = rt.graph, rt.B
+        N, H, W = mv.N, mv.H, mv.W
+        act = B.act_dtype
+        warp_frame = None
+        if want_warp_frame:
+            warp_frame = B.warp(B.from_nchw(dpb["ref_frame"], dtype=F32), mv)
+        mv2 = B.flow_down2(mv, gain=0.5)
+        mv3 = B.flow_down2(mv2, gain=0.5)
+        f1, f2, f3 = self.multi_scale_feature_extractor(dpb)
+        cat_a = B.new(N, H // 2, W // 2, 128, dtype=act)    # (context3_up | context2)
+        cat_b = B.new(N, H, W, 128, dtype=act)              # (context2_up | context1)
+        c1 = B.warp(f1, mv, out=cat_b.sl(64, 128))
+        c2 = B.warp(f2, mv2, out=cat_a.sl(64, 128))
+        c3 = B.warp(f3, mv3)
+        ctx = self._ctx_buffer(rt, N, H, W)
+        e2 = B.new(N, H // 2, W // 2, 128, dtype=act)
+        e3 = B.new(N, H // 4, W // 4, 128, dtype=act)
+        n = "context_fusion_net"
+        t = g.conv(n + ".conv3_up.0", c3, ps=True)
+        g.res_block(n + ".res_block3_up", t, out=cat_a.sl(0, 64))
+        g.res_block(n + ".res_block3_out", g.conv(n + ".conv3_out", c3), res2=c3, out=e3.sl(64, 128))
+        t = g.conv(n + ".conv2_up.0", cat_a, ps=True)
+        g.res_block(n + ".res_block2_up", t, out=cat_b.sl(0, 64))
+        g.res_block(n + ".res_block2_out", g.conv(n + ".conv2_out", cat_a), res2=c2, out=e2.sl(64, 128))
+        g.res_block(n + ".res_block1_out", g.conv(n + ".conv1_out", cat_b), res2=c1, out=ctx.sl(32, 96))
+        return ctx, e2, e3, warp_frame
+
+    def _mv_prior(self, rt, mv_z_hat, dpb):
+        """mv hyper decoder + prior fusion (video_model.py:285-293 / :371-380)."""
+        g, B = rt.graph, rt.B
+        N, h, w = mv_z_hat.N, mv_z_hat.H * 4, mv_z_hat.W * 4
+        fin = B.new(N, h, w, 192, zero=dpb["ref_mv_y"] is None)
+        g.hyper_synthesis("mv_hyper_prior_decoder", mv_z_hat, out=fin.sl(0, 128))
+        if dpb["ref_mv_y"] is not None:
+            B.from_nchw(dpb["ref_mv_y"], out=fin.sl(128, 192))
+        return g.three_convs("mv_y_prior_fusion", fin)
+
+    def _y_prior(self, rt, z_hat, e3, dpb):
+        """hierarchical + temporal prior -> fusion (video_model.py:312-322 / :394-405)."""
+        g, B = rt.graph, rt.B
+        N, h, w = z_hat.N, z_hat.H * 4, z_hat.W * 4
+        fin = B.new(N, h, w, 480, zero=dpb["ref_y"] is None)
+        t = g.conv("temporal_prior_encoder.0", e3.sl(64, 128), stride=2, post=0.1)
+        g.conv("temporal_prior_encoder.2", t, stride=2, out=fin.sl(0, 192))
+        g.hyper_synthesis("contextual_hyper_prior_decoder", z_hat, out=fin.sl(192, 384))
+        if dpb["ref_y"] is not None:
+            B.from_nchw(dpb["ref_y"], out=fin.sl(384, 480))
+        return g.three_convs("y_prior_fusion", fin)
+
+    def _contextual_encoder(self, rt, ctx, e2, e3):
+        """video_model.py:71-90; x already sits in ctx[96:99)."""
+        g = rt.graph
+        n = "contextual_encoder"
+        m = self._enc_in_map(rt)
+        g.conv(n + ".conv1", ctx.sl(32, 32 + len(m)), in_map=m, stride=2, out=e2.sl(0, 64))
+        f = g.res_block(n + ".res1", e2, 0.1, True, True)
+        g.conv(n + ".conv2", f, stride=2, out=e3.sl(0, 64))
+        f = g.res_block(n + ".res2", e3, 0.1, True, True)
+        f = g.conv(n + ".conv3", f, stride=2)
+        return g.conv(n + ".conv4", f, stride=2)
+
+    def _reconstruct(self, rt, y_hat, ctx, e2, e3):
+        """ContextualDecoder (video_model.py:93-112) + ReconGeneration (:115-128)."""
+        g = rt.graph
+        n = "contextual_decoder"
+        f = g.conv(n + ".up1.0", y_hat, ps=True)
+        g.conv(n + ".up2.0", f, ps=True, out=e3.sl(0, 64))
+        f = g.res_block(n + ".res1", e3, 0.1, True, True)
+        g.conv(n + ".up3.0", f, ps=True, out=e2.sl(0, 64))
+        f = g.res_block(n + ".res2", e2, 0.1, True, True)
+        g.conv(n + ".up4.0", f, ps=True, out=ctx.sl(0, 32))
+        n = "recon_generation_net"
+        f = g.conv(n + ".first_conv", ctx.sl(0, 96))
+        f = g.unet(n + ".unet_1", f)
+        feature = g.unet(n + ".unet_2", f)
+        x_hat = g.conv(n + ".recon_conv", feature, out_dtype=F32)
+        return feature, x_hat
+
+    def _analyse(self, x, dpb, mv_y_q_scale, y_q_scale, want_full):
+        """Encoder-side trunk shared by compress() and forward_one_frame() (video_model.py:263-331 /
+        :470-538)."""
+        rt = self._runtime()
+        g, B = rt.graph, rt.B
+        N, _, H, W = x.shape
+        q_mv = self._curr_q(rt, self.mv_y_q_basic, mv_y_q_scale, N)
+        q_y = self._curr_q(rt, self.y_q_basic, y_q_scale, N)
+        table = self._scale_table
+
+        est_mv = g.spynet("optic_flow", x, dpb["ref_frame"])
+        mv_y = B.scale(g.analysis("mv_encoder", est_mv), q_mv, "div")
+        mv_z = g.hyper_analysis("mv_hyper_prior_encoder", mv_y)
+        zs = (N, 64, mv_z.H, mv_z.W)
+        mv_z_sym = B.empty(zs, torch.int16)
+        mv_z_hat = B.round_latent(mv_z, sym=mv_z_sym)
+        mv_fusion = self._mv_prior(rt, mv_z_hat, dpb)
+        mv_dp = g.dual_prior_encode(table, mv_y, mv_fusion, "mv_y_spatial_prior", q_mv, want_full)
+        mv_y_hat = mv_dp["y_hat"]
+        mv_hat = g.synthesis("mv_decoder", mv_y_hat, out_dtype=F32)
+
+        ctx, e2, e3, warp_frame = self.motion_compensation(dpb, mv_hat, want_warp_frame=want_full)
+        B.from_nchw(x, out=ctx.sl(96, 99))
+        y = B.scale(self._contextual_encoder(rt, ctx, e2, e3), q_y, "div")
+        n = "contextual_hyper_prior_encoder"
+        t = g.conv(n + ".0", y, post=0.01)
+        t = g.conv(n + ".2", t, stride=2, post=0.01)
+        z = g.conv(n + ".4", t, stride=2)
+        z_sym = B.empty(zs, torch.int16)
+        z_hat = B.round_latent(z, sym=z_sym)
+        y_fusion = self._y_prior(rt, z_hat, e3, dpb)
+        y_dp = g.dual_prior_encode(table, y, y_fusion, "y_spatial_prior", q_y, want_full)
+        y_hat = y_dp["y_hat"]
+        feature, x_hat = self._reconstruct(rt, y_hat, ctx, e2, e3)
+        return dict(mv_z_sym=mv_z_sym, z_sym=z_sym, mv_z_hat=mv_z_hat, z_hat=z_hat, mv_dp=mv_dp, y_dp=y_dp,
+                    mv_y_hat=mv_y_hat, y_hat=y_hat, feature=feature, x_hat=x_hat, warp_frame=warp_frame,
+                    est_mv=est_mv, mv_hat=mv_hat)
+
+    # ---- public API ------------------------------------------------------------------------------
+    @torch.no_grad()
+    def compress(self, x, dpb, mv_y_q_scale, y_q_scale):
+        """video_model.py:263-352.  Stream order: z_mv, mv_y pass 0/1, z, y pass 0/1 (:333-340)."""
+        rt = self._need_coder()
+        assert x.shape[0] == 1, "the bitstream path is batch 1 (entropy_models.py:186)"
+        B = rt.B
+        t = self._analyse(x, dpb, mv_y_q_scale, y_q_scale, want_full=False)
+        host = self._to_host(t["mv_z_sym"], *t["mv_dp"]["sym"], *t["mv_dp"]["idx"],
+                             t["z_sym"], *t["y_dp"]["sym"], *t["y_dp"]["idx"])
+        mv_z, ms0, ms1, mi0, mi1, z, ys0, ys1, yi0, yi1 = host
+        c = rt.coder
+        c.reset_encoder()
+        c.encode_channels(mv_z, rt.tables["bit_estimator_z_mv"])
+        c.encode_planes(ms0, mi0, rt.tables["y"])
+        c.encode_planes(ms1, mi1, rt.tables["y"])
+        c.encode_channels(z, rt.tables["bit_estimator_z"])
+        c.encode_planes(ys0, yi0, rt.tables["y"])
+        c.encode_planes(ys1, yi1, rt.tables["y"])
+        bit_stream = c.flush_encoder()
+        self._last_symbols = dict(mv_z=mv_z, mv_y_q_w_0=ms0, mv_y_q_w_1=ms1, mv_idx_0=mi0, mv_idx_1=mi1,
+                                  z=z, y_q_w_0=ys0, y_q_w_1=ys1, y_idx_0=yi0, y_idx_1=yi1)
+        return {
+            "dbp": {
+                "ref_frame": B.to_nchw(t["x_hat"]),
+                "ref_feature": B.to_nchw(t["feature"]),
+                "ref_y": B.to_nchw(t["y_hat"]),
+                "ref_mv_y": B.to_nchw(t["mv_y_hat"]),
+            },
+            "bit_stream": bit_stream,
+        }
+
+    @torch.no_grad()
+    def decompress(self, dpb, string, height, width, mv_y_q_scale, y_q_scale):
+        """video_model.py:354-422."""
+        rt = self._need_coder()
+        g, B = rt.graph, rt.B
+        q_mv = self._curr_q(rt, self.mv_y_q_basic, mv_y_q_scale, 1)
+        q_y = self._curr_q(rt, self.y_q_basic, y_q_scale, 1)
+        table = self._scale_table
+        rt.coder.set_stream(string)
+        zs = get_downsampled_shape(height, width, 64)
+        dec = self._decode_plane_fn(rt)
+
+        mv_z_hat = self._decode_z(rt, "bit_estimator_z_mv", 64, zs)
+        mv_fusion = self._mv_prior(rt, mv_z_hat, dpb)
+        mv_y_hat = g.dual_prior_decode(table, mv_fusion, 64, "mv_y_spatial_prior", q_mv, dec)
+        mv_hat = g.synthesis("mv_decoder", mv_y_hat, out_dtype=F32)
+        ctx, e2, e3, _ = self.motion_compensation(dpb, mv_hat)
+        z_hat = self._decode_z(rt, "bit_estimator_z", 64, zs)
+        y_fusion = self._y_prior(rt, z_hat, e3, dpb)
+        y_hat = g.dual_prior_decode(table, y_fusion, 96, "y_spatial_prior", q_y, dec)
+        feature, x_hat = self._reconstruct(rt, y_hat, ctx, e2, e3)
+        return {
+            "dpb": {
+                "ref_frame": B.to_nchw(x_hat, clamp=(0.0, 1.0)),
+                "ref_feature": B.to_nchw(feature),
+                "ref_y": B.to_nchw(y_hat),
+                "ref_mv_y": B.to_nchw(mv_y_hat),
+            }
+        }
+
+    def encode_decode_bytes(self, x, dpb, pic_height, pic_width, mv_y_q_scale, y_q_scale):
+        """encode_decode(write) with the `.bin` kept in memory: returns (result, blob)."""
+        mv_y_q_scale, mv_y_q_index = get_rounded_q(mv_y_q_scale)
+        y_q_scale, y_q_index = get_rounded_q(y_q_scale)
+        t0 = time.time()
+        encoded = self.compress(x, dpb, mv_y_q_scale, y_q_scale)
+        blob = pack_p(encoded["bit_stream"], mv_y_q_index, y_q_index)
+        t1 = time.time()
+        a, b, string = unpack_p(blob)
+        decoded = self.decompress(dpb, string, pic_height, pic_width, a / 100, b / 100)
+        t2 = time.time()
+        return {"dpb": decoded["dpb"], "bit": len(blob) * 8, "encoding_time": t1 - t0,
+                "decoding_time": t2 - t1}, blob
+
+    def encode_decode(self, x, dpb, output_path=None, pic_width=None, pic_height=None,
+                      mv_y_q_scale=None, y_q_scale=None):
+        """video_model.py:424-468."""
+        if output_path is not None:
+            mv_y_q_scale, mv_y_q_index = get_rounded_q(mv_y_q_scale)
+            y_q_scale, y_q_index = get_rounded_q(y_q_scale)
+            t0 = time.time()
+            encoded = self.compress(x, dpb, mv_y_q_scale, y_q_scale)
+            encode_p(encoded["bit_stream"], mv_y_q_index, y_q_index, output_path)
+            bits = filesize(output_path) * 8
+            t1 = time.time()
+            mv_y_q_index, y_q_index, string = decode_p(output_path)
+            decoded = self.decompress(dpb, string, pic_height, pic_width,
+                                      mv_y_q_index / 100, y_q_index / 100)
+            t2 = time.time()
+            return {"dpb": decoded["dpb"], "bit": bits, "encoding_time": t1 - t0,
+                    "decoding_time": t2 - t1}
+        encoded = self.forward_one_frame(x, dpb, mv_y_q_scale=mv_y_q_scale, y_q_scale=y_q_scale)
+        return {
+            "dpb": encoded["dpb"],
+            "bit_y": encoded["bit_y"].item(),
+            "bit_z": encoded["bit_z"].item(),
+            "bit_mv_y": encoded["bit_mv_y"].item(),
+            "bit_mv_z": encoded["bit_mv_z"].item(),
+            "bit": encoded["bit"].item(),
+            "decoding_time": 0,
+        }
+
+    def forward_one_frame(self, x, dpb, mv_y_q_scale=None, y_q_scale=None):
+        """video_model.py:470-592 (eval mode: quant = round, bits from the likelihood kernels)."""
+        if self.training and torch.is_grad_enabled():
+            raise NotImplementedError(
+                "vcm_ts_b200.DMC: the training path (autograd through the CUDA kernels, noise "
+                "quantisation) is not built yet; call .eval() / torch.no_grad()")
+        with torch.no_grad():
+            rt = self._runtime()
+            B = rt.B
+            t = self._analyse(x, dpb, mv_y_q_scale, y_q_scale, want_full=True)
+            N, _, H, W = x.shape
+            pixel_num = H * W
+            x_hat = B.to_nchw(t["x_hat"])
+            mse = B.sq_err_sum(x, x_hat) / pixel_num
+            me_mse = B.sq_err_sum(x, B.to_nchw(t["warp_frame"])) / pixel_num
+            bpp_y = B.latent_bits(t["y_dp"]["y_q"], t["y_dp"]["scales_hat"], N, "laplace") / pixel_num
+            bpp_mv_y = B.latent_bits(t["mv_dp"]["y_q"], t["mv_dp"]["scales_hat"], N, "laplace") / pixel_num
+            bpp_z = B.factorized_bits(t["z_hat"], self._fparams(rt, "bit_estimator_z")) / pixel_num
+            bpp_mv_z = B.factorized_bits(t["mv_z_hat"], self._fparams(rt, "bit_estimator_z_mv")) / pixel_num
+            bpp = bpp_y + bpp_z + bpp_mv_y + bpp_mv_z
+            return {
+                "bpp_mv_y": bpp_mv_y, "bpp_mv_z": bpp_mv_z, "bpp_y": bpp_y, "bpp_z": bpp_z, "bpp": bpp,
+                "me_mse": me_mse, "mse": mse,
+                "dpb": {"ref_frame": x_hat, "ref_feature": B.to_nchw(t["feature"]),
+                        "ref_y": B.to_nchw(t["y_hat"]), "ref_mv_y": B.to_nchw(t["mv_y_hat"])},
+                "bit": torch.sum(bpp) * pixel_num, "bit_y": torch.sum(bpp_y) * pixel_num,
+                "bit_z": torch.sum(bpp_z) * pixel_num, "bit_mv_y": torch.sum(bpp_mv_y) * pixel_num,
+                "bit_mv_z": torch.sum(bpp_mv_z) * pixel_num,
+            }
+
+    def forward(self, x, dpb, mv_y_q_scale=None, y_q_scale=None):
+        return self.forward_one_frame(x, dpb, mv_y_q_scale=mv_y_q_scale, y_q_scale=y_q_scale)
+
+
+# ==========================================================================================
+# I-frame model
+# ==========================================================================================
+class IntraNoAR(CompressionModel):
+    """image_model.py:16-200."""
+
+    def __init__(self, N=192, anchor_num=4, precision=None):
+        super().__init__(arch.intra_spec(N, anchor_num), "gaussian", precision)
+        self.N = int(N)
+        self.anchor_num = int(anchor_num)
+
+    @staticmethod
+    def get_q_scales_from_ckpt(ckpt_path):
+        return get_state_dict(ckpt_path)["q_scale"].reshape(-1)
+
+    def get_curr_q(self, q_scale):
+        return torch.max(self.q_basic, torch.ones_like(self.q_basic) * 0.5) * q_scale
+
+    def _trunk(self, rt, x, q, want_full):
+        g, B = rt.graph, rt.B
+        y = B.scale(g.analysis("enc", B.from_nchw(x)), q, "div")
+        z = g.hyper_analysis("hyper_enc", y)
+        z_sym = B.empty((x.shape[0], self.N, z.H, z.W), torch.int16)
+        z_hat = B.round_latent(z, sym=z_sym)
+        fusion = g.three_convs("y_prior_fusion", g.hyper_synthesis("hyper_dec", z_hat))
+        dp = g.dual_prior_encode(self._scale_table, y, fusion, "y_spatial_prior", q, want_full)
+        return z_sym, z_hat, dp
+
+    def _synth(self, rt, y_hat):
+        g = rt.graph
+        t = g.synthesis("dec", y_hat)
+        return g.conv("refine.1", g.unet("refine.0", t), out_dtype=F32)
+
+    def forward(self, x, q_scale=None):
+        """image_model.py:54-105 (eval mode)."""
+        if self.training and torch.is_grad_enabled():
+            raise NotImplementedError("vcm_ts_b200.IntraNoAR: training path not built; use eval()/no_grad()")
+        with torch.no_grad():
+            rt = self._runtime()
+            B = rt.B
+            N, _, H, W = x.shape
+            q = self._curr_q(rt, self.q_basic, q_scale, N)
+            _, z_hat, dp = self._trunk(rt, x, q, True)
+            x_hat = B.to_nchw(self._synth(rt, dp["y_hat"]))
+            pixel_num = H * W
+            bpp_y = B.latent_bits(dp["y_q"], dp["scales_hat"], N, "gaussian") / pixel_num
+            bpp_z = B.factorized_bits(z_hat, self._fparams(rt, "bit_estimator_z")) / pixel_num
+            mse = B.sq_err_sum(x, x_hat) / pixel_num
+            bits = torch.sum(bpp_y + bpp_z) * pixel_num
+            return {"x_hat": x_hat, "mse": mse, "bit": bits.item(), "bpp": bpp_y + bpp_z,
+                    "bpp_y": bpp_y, "bpp_z": bpp_z}
+
+    @torch.no_grad()
+    def compress(self, x, q_scale):
+        """image_model.py:148-177.  Stream order: z, y pass 0, y pass 1."""
+        rt = self._need_coder()
+        assert x.shape[0] == 1, "the bitstream path is batch 1 (entropy_models.py:186)"
+        q = self._curr_q(rt, self.q_basic, q_scale, 1)
+        z_sym, _, dp = self._trunk(rt, x, q, False)
+        z, s0, s1, i0, i1 = self._to_host(z_sym, *dp["sym"], *dp["idx"])
+        c = rt.coder
+        c.reset_encoder()
+        c.encode_channels(z, rt.tables["bit_estimator_z"])
+        c.encode_planes(s0, i0, rt.tables["y"])
+        c.encode_planes(s1, i1, rt.tables["y"])
+        self._last_symbols = dict(z=z, y_q_w_0=s0, y_q_w_1=s1, y_idx_0=i0, y_idx_1=i1)
+        return {"bit_stream": c.flush_encoder()}
+
+    @torch.no_grad()
+    def decompress(self, bit_stream, height, width, q_scale):
+        """image_model.py:179-200."""
+        rt = self._need_coder()
+        g, B = rt.graph, rt.B
+        q = self._curr_q(rt, self.q_basic, q_scale, 1)
+        rt.coder.set_stream(bit_stream)
+        zs = get_downsampled_shape(height, width, 64)
+        z_hat = self._decode_z(rt, "bit_estimator_z", self.N, zs)
+        fusion = g.three_convs("y_prior_fusion", g.hyper_synthesis("hyper_dec", z_hat))
+        y_hat = g.dual_prior_decode(self._scale_table, fusion, self.N, "y_spatial_prior", q,
+                                    self._decode_plane_fn(rt))
+        return {"x_hat": B.to_nchw(self._synth(rt, y_hat), clamp=(0.0, 1.0))}
+
+    def encode_decode_bytes(self, x, q_scale, pic_height, pic_width):
+        t0 = time.time()
+        q_scale, q_index = get_rounded_q(q_scale)
+        blob = pack_i(pic_height, pic_width, q_index, self.compress(x, q_scale)["bit_stream"])
+        t1 = time.time()
+        height, width, q_index, bit_stream = unpack_i(blob)
+        x_hat = self.decompress(bit_stream, height, width, q_index / 100)["x_hat"]
+        t2 = time.time()
+        return {"bit": len(blob) * 8, "x_hat": x_hat, "encoding_time": t1 - t0,
+                "decoding_time": t2 - t1}, blob
+
+    def encode_decode(self, x, q_scale, output_path=None, pic_width=None, pic_height=None):
+        """image_model.py:114-146."""
+        if output_path is None:
+            return self.forward(x, q_scale)
+        assert pic_height is not None
+        assert pic_width is not None
+        t0 = time.time()
+        q_scale, q_index = get_rounded_q(q_scale)
+        bit_stream = self.compress(x, q_scale)["bit_stream"]
+        encode_i(pic_height, pic_width, q_index, bit_stream, output_path)
+        bit = filesize(output_path) * 8
+        t1 = time.time()
+        height, width, q_index, bit_stream = decode_i(output_path)
+        x_hat = self.decompress(bit_stream, height, width, q_index / 100)["x_hat"]
+        t2 = time.time()
+        return {"bit": bit, "x_hat": x_hat, "encoding_time": t1 - t0, "decoding_time": t2 - t1}
