@@ -21,6 +21,9 @@ class EmulBackend:
     def __init__(self, device="cpu", precision="fp32"):
         self.device = torch.device(device)
         self.launches = 0
+        # "twin": fp32 math but the bf16-mode graph (activated twins instead of pre-activations)
+        self.use_twin = precision != "fp32"
+        self.tc_like = []      # (name-less) record of convs that asked for a pre-activation
 
     def new(self, N, H, W, C, dtype=None, zero=False):
         f = torch.zeros if zero else (lambda s, dtype: torch.full(s, float("nan"), dtype=dtype))
@@ -50,8 +53,10 @@ class EmulBackend:
         v.dense().copy_(t_nchw.permute(0, 2, 3, 1).to(v.dtype))
 
     def conv(self, x, pc, out=None, stride=1, pre=None, post=None, res=None, res_scale=None,
-             res2=None, ps=False, out_dtype=None):
+             res2=None, ps=False, out_dtype=None, slope2=None, out2=None):
         assert x.C == pc.Cin
+        if pre is not None:
+            self.tc_like.append((pc.K, pc.Cin, pc.Cout))
         t = self._nchw(x)
         assert not torch.isnan(t).any(), "conv reads an unwritten buffer"
         if pre is not None:
@@ -72,6 +77,11 @@ class EmulBackend:
         assert (out.N, out.C, out.H, out.W) == tuple(y.shape)
         self._store(out, y)
         self.launches += 1
+        if slope2 is not None:
+            if out2 is None:
+                out2 = self.new(y.shape[0], y.shape[2], y.shape[3], y.shape[1], dtype=out.dtype)
+            self._store(out2, F.leaky_relu(y, slope2))
+            return out, out2
         return out
 
     def from_nchw(self, t, out=None, dtype=None):

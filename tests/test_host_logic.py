@@ -35,15 +35,18 @@ def test_state_dict_layout_matches_reference_tree():
         assert got == want
 
 
-@pytest.fixture(scope="module")
-def models():
+@pytest.fixture(scope="module", params=["fp32", "twin"])
+def models(request):
+    """'twin' = the bf16-mode graph (activated twins instead of pre-activations) in fp32 math."""
     torch.set_num_threads(THREADS)
-    dmc, intra = DMC().eval(), IntraNoAR().eval()
+    dmc, intra = DMC(precision=request.param).eval(), IntraNoAR(precision=request.param).eval()
     dmc.load_state_dict(fixture.fixture_state_dict(O.state_shapes("dmc")), strict=True)
     intra.load_state_dict(fixture.fixture_state_dict(O.state_shapes("intra")), strict=True)
     for m in (dmc, intra):
         m._backend_factory = lambda dev, prec: EmulBackend(dev, prec)
         m.update(force=True)
+    if request.param == "twin":
+        assert dmc._rt.B.use_twin
     return dmc, intra
 
 
@@ -67,7 +70,7 @@ def test_gop_prefix_through_host_logic(models, golden_dir, tmp_path):
     x0 = _pad64(fr[0:1].float() / 255.0)
     r, blob = intra.encode_decode_bytes(x0, qi, ph, pw)
     assert blob == G["i_bin"].tobytes()
-    assert np.array_equal(r["x_hat"].numpy(), G["i_x_hat"])
+    np.testing.assert_allclose(r["x_hat"].numpy(), G["i_x_hat"], atol=2e-5)
     # file-based public call gives the same bytes
     path = str(tmp_path / "i.bin")
     r2 = intra.encode_decode(x0, qi, output_path=path, pic_width=pw, pic_height=ph)
@@ -99,10 +102,12 @@ def test_gop_prefix_through_host_logic(models, golden_dir, tmp_path):
         assert open(path, "rb").read() == G[p + "bin"].tobytes()
         assert r["bit"] == int(G[p + "bit"][0])
         d = r["dpb"]
-        assert np.array_equal(d["ref_frame"].numpy(), G[p + "ref_frame"])
-        assert np.array_equal(d["ref_y"].numpy(), G[p + "ref_y"])
-        assert np.array_equal(d["ref_mv_y"].numpy(), G[p + "ref_mv_y"])
-        assert np.array_equal(d["ref_feature"].numpy(), G[p + "ref_feature"])
+        # float tensors: the emulation feeds strided NHWC views to oneDNN, so accumulation order
+        # differs from the reference's NCHW calls in the last bits; integers above are exact
+        np.testing.assert_allclose(d["ref_frame"].numpy(), G[p + "ref_frame"], atol=5e-5)
+        np.testing.assert_allclose(d["ref_y"].numpy(), G[p + "ref_y"], atol=1e-4)
+        np.testing.assert_allclose(d["ref_mv_y"].numpy(), G[p + "ref_mv_y"], atol=1e-4)
+        np.testing.assert_allclose(d["ref_feature"].numpy(), G[p + "ref_feature"], atol=1e-3, rtol=1e-4)
         dpb = d
 
 

@@ -75,6 +75,9 @@ class CudaBackend:
             raise ValueError("precision must be 'fp32' or 'bf16'")
         self.precision = precision
         self.act_dtype = torch.float32 if precision == "fp32" else torch.bfloat16
+        # bf16 mode: producers also store the activated twin a following ResBlock reads, so the
+        # tensor-core engine never needs a pre-activation on TMA-loaded tiles
+        self.use_twin = precision == "bf16"
         self.launches = 0
 
     # -- plumbing -------------------------------------------------------------------------
@@ -114,7 +117,9 @@ class CudaBackend:
 
     # -- convolution ------------------------------------------------------------------------
     def conv(self, x, pc, out=None, stride=1, pre=None, post=None, res=None, res_scale=None,
-             res2=None, ps=False, out_dtype=None):
+             res2=None, ps=False, out_dtype=None, slope2=None, out2=None):
+        """Fused conv.  With slope2 set, also stores leaky_relu(y, slope2) to `out2` and returns
+        (y, y_act)."""
         K = pc.K
         assert x.C == pc.Cin, f"conv input has {x.C} channels, weights expect {pc.Cin}"
         pad = K // 2
@@ -140,12 +145,20 @@ class CudaBackend:
         if res2 is not None:
             flags |= _lib.CONV_RES2
             assert (res2.N, res2.H, res2.W, res2.C) == (out.N, out.H, out.W, out.C) and res2.dtype == out.dtype
+        if slope2 is not None:
+            flags |= _lib.CONV_OUT2
+            if out2 is None:
+                out2 = self.new(out.N, out.H, out.W, out.C, dtype=out.dtype)
+            assert (out2.N, out2.H, out2.W, out2.C) == (out.N, out.H, out.W, out.C) and out2.dtype == out.dtype
         d = ConvDesc(x.N, x.H, x.W, pc.Cin, pc.Cout, K, stride, x.cs, out.cs,
-                     res.cs if res is not None else 0, res2.cs if res2 is not None else 0, flags,
-                     float(pre or 0.0), float(post or 0.0), _code(x.dtype), _code(out.dtype))
+                     res.cs if res is not None else 0, res2.cs if res2 is not None else 0,
+                     out2.cs if slope2 is not None else 0, flags,
+                     float(pre or 0.0), float(post or 0.0), float(slope2 or 0.0),
+                     _code(x.dtype), _code(out.dtype))
         args = (ctypes.byref(d), x.ptr, None, pc.bias.data_ptr(), res.ptr if res is not None else None,
                 res_scale.data_ptr() if res_scale is not None else None,
-                res2.ptr if res2 is not None else None, out.ptr, self.stream)
+                res2.ptr if res2 is not None else None, out.ptr,
+                out2.ptr if slope2 is not None else None, self.stream)
         if pc.w_umma is not None and self.L.vcm_conv2d_tc_supported(ctypes.byref(d)) == 1:
             a = list(args)
             a[2] = pc.w_umma.data_ptr()
@@ -155,7 +168,7 @@ class CudaBackend:
             a[2] = pc.w.data_ptr()
             check(self.L.vcm_conv2d_fwd(*a), "vcm_conv2d_fwd")
         self.launches += 1
-        return out
+        return (out, out2) if slope2 is not None else out
 
     # -- layout / elementwise ---------------------------------------------------------------
     def from_nchw(self, t, out=None, dtype=None):

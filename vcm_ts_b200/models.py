@@ -263,15 +263,19 @@ class DMC(CompressionModel):
             f = g.conv("feature_adaptor_I", B.from_nchw(dpb["ref_frame"]))
         else:
             f = g.conv("feature_adaptor_P", B.from_nchw(dpb["ref_feature"]))
-        l1 = g.res_block("feature_extractor.res_block1", g.conv("feature_extractor.conv1", f))
-        l2 = g.res_block("feature_extractor.res_block2", g.conv("feature_extractor.conv2", l1, stride=2))
-        l3 = g.res_block("feature_extractor.res_block3", g.conv("feature_extractor.conv3", l2, stride=2))
+        t, ta = g.conv_t("feature_extractor.conv1", f, 0.01)
+        l1 = g.res_block("feature_extractor.res_block1", t, x_act=ta)
+        t, ta = g.conv_t("feature_extractor.conv2", l1, 0.01, stride=2)
+        l2 = g.res_block("feature_extractor.res_block2", t, x_act=ta)
+        t, ta = g.conv_t("feature_extractor.conv3", l2, 0.01, stride=2)
+        l3 = g.res_block("feature_extractor.res_block3", t, x_act=ta)
         return l1, l2, l3
 
     def motion_compensation(self, dpb, mv, want_warp_frame=False):
         """video_model.py:233-246 + MultiScaleContextFusion :40-68.  mv: fp32 flow view.
         Returns (ctx buffer holding context1 at [32,96), E2 = [f | context2], E3 = [f | context3],
-        warp_frame view or None)."""
+        warp_frame view or None).  E2 / E3 are (plain, activated-twin-or-None) pairs: the twins
+        (LeakyReLU 0.1) feed the bottleneck ResBlocks of the contextual encoder / decoder."""
         rt = self._runtime()
         g, B = rt.graph, rt.B
         N, H, W = mv.N, mv.H, mv.W
@@ -290,15 +294,23 @@ class DMC(CompressionModel):
         ctx = self._ctx_buffer(rt, N, H, W)
         e2 = B.new(N, H // 2, W // 2, 128, dtype=act)
         e3 = B.new(N, H // 4, W // 4, 128, dtype=act)
+        e2a = B.new(N, H // 2, W // 2, 128, dtype=act) if B.use_twin else None
+        e3a = B.new(N, H // 4, W // 4, 128, dtype=act) if B.use_twin else None
+        tw = 0.1 if B.use_twin else None
         n = "context_fusion_net"
-        t = g.conv(n + ".conv3_up.0", c3, ps=True)
-        g.res_block(n + ".res_block3_up", t, out=cat_a.sl(0, 64))
-        g.res_block(n + ".res_block3_out", g.conv(n + ".conv3_out", c3), res2=c3, out=e3.sl(64, 128))
-        t = g.conv(n + ".conv2_up.0", cat_a, ps=True)
-        g.res_block(n + ".res_block2_up", t, out=cat_b.sl(0, 64))
-        g.res_block(n + ".res_block2_out", g.conv(n + ".conv2_out", cat_a), res2=c2, out=e2.sl(64, 128))
-        g.res_block(n + ".res_block1_out", g.conv(n + ".conv1_out", cat_b), res2=c1, out=ctx.sl(32, 96))
-        return ctx, e2, e3, warp_frame
+        t, ta = g.conv_t(n + ".conv3_up.0", c3, 0.01, ps=True)
+        g.res_block(n + ".res_block3_up", t, x_act=ta, out=cat_a.sl(0, 64))
+        t, ta = g.conv_t(n + ".conv3_out", c3, 0.01)
+        g.res_block(n + ".res_block3_out", t, x_act=ta, res2=c3, out=e3.sl(64, 128), twin_out=tw,
+                    out2=e3a.sl(64, 128) if e3a else None)
+        t, ta = g.conv_t(n + ".conv2_up.0", cat_a, 0.01, ps=True)
+        g.res_block(n + ".res_block2_up", t, x_act=ta, out=cat_b.sl(0, 64))
+        t, ta = g.conv_t(n + ".conv2_out", cat_a, 0.01)
+        g.res_block(n + ".res_block2_out", t, x_act=ta, res2=c2, out=e2.sl(64, 128), twin_out=tw,
+                    out2=e2a.sl(64, 128) if e2a else None)
+        t, ta = g.conv_t(n + ".conv1_out", cat_b, 0.01)
+        g.res_block(n + ".res_block1_out", t, x_act=ta, res2=c1, out=ctx.sl(32, 96))
+        return ctx, (e2, e2a), (e3, e3a), warp_frame
 
     def _mv_prior(self, rt, mv_z_hat, dpb):
         """mv hyper decoder + prior fusion (video_model.py:285-293 / :371-380)."""
@@ -315,7 +327,7 @@ class DMC(CompressionModel):
         g, B = rt.graph, rt.B
         N, h, w = z_hat.N, z_hat.H * 4, z_hat.W * 4
         fin = B.new(N, h, w, 480, zero=dpb["ref_y"] is None)
-        t = g.conv("temporal_prior_encoder.0", e3.sl(64, 128), stride=2, post=0.1)
+        t = g.conv("temporal_prior_encoder.0", e3[0].sl(64, 128), stride=2, post=0.1)
         g.conv("temporal_prior_encoder.2", t, stride=2, out=fin.sl(0, 192))
         g.hyper_synthesis("contextual_hyper_prior_decoder", z_hat, out=fin.sl(192, 384))
         if dpb["ref_y"] is not None:
@@ -327,10 +339,12 @@ class DMC(CompressionModel):
         g = rt.graph
         n = "contextual_encoder"
         m = self._enc_in_map(rt)
-        g.conv(n + ".conv1", ctx.sl(32, 32 + len(m)), in_map=m, stride=2, out=e2.sl(0, 64))
-        f = g.res_block(n + ".res1", e2, 0.1, True, True)
-        g.conv(n + ".conv2", f, stride=2, out=e3.sl(0, 64))
-        f = g.res_block(n + ".res2", e3, 0.1, True, True)
+        (e2, e2a), (e3, e3a) = e2, e3
+        g.conv_t(n + ".conv1", ctx.sl(32, 32 + len(m)), 0.1, in_map=m, stride=2, out=e2.sl(0, 64),
+                 out2=e2a.sl(0, 64) if e2a else None)
+        f = g.res_block(n + ".res1", e2, 0.1, True, True, x_act=e2a)
+        g.conv_t(n + ".conv2", f, 0.1, stride=2, out=e3.sl(0, 64), out2=e3a.sl(0, 64) if e3a else None)
+        f = g.res_block(n + ".res2", e3, 0.1, True, True, x_act=e3a)
         f = g.conv(n + ".conv3", f, stride=2)
         return g.conv(n + ".conv4", f, stride=2)
 
@@ -338,11 +352,12 @@ class DMC(CompressionModel):
         """ContextualDecoder (video_model.py:93-112) + ReconGeneration (:115-128)."""
         g = rt.graph
         n = "contextual_decoder"
+        (e2, e2a), (e3, e3a) = e2, e3
         f = g.conv(n + ".up1.0", y_hat, ps=True)
-        g.conv(n + ".up2.0", f, ps=True, out=e3.sl(0, 64))
-        f = g.res_block(n + ".res1", e3, 0.1, True, True)
-        g.conv(n + ".up3.0", f, ps=True, out=e2.sl(0, 64))
-        f = g.res_block(n + ".res2", e2, 0.1, True, True)
+        g.conv_t(n + ".up2.0", f, 0.1, ps=True, out=e3.sl(0, 64), out2=e3a.sl(0, 64) if e3a else None)
+        f = g.res_block(n + ".res1", e3, 0.1, True, True, x_act=e3a)
+        g.conv_t(n + ".up3.0", f, 0.1, ps=True, out=e2.sl(0, 64), out2=e2a.sl(0, 64) if e2a else None)
+        f = g.res_block(n + ".res2", e2, 0.1, True, True, x_act=e2a)
         g.conv(n + ".up4.0", f, ps=True, out=ctx.sl(0, 32))
         n = "recon_generation_net"
         f = g.conv(n + ".first_conv", ctx.sl(0, 96))

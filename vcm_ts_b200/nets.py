@@ -25,12 +25,28 @@ class Graph:
     def conv(self, name, x, in_map=None, **kw):
         return self.B.conv(x, self.pc(name, in_map), **kw)
 
+    def conv_t(self, name, x, slope2, out=None, out2=None, **kw):
+        """Conv whose output feeds a ResBlock: returns (y, y_act).  y_act = leaky_relu(y, slope2)
+        is stored by the same epilogue when the backend runs the twin graph (bf16 mode), else None."""
+        if not self.B.use_twin:
+            return self.conv(name, x, out=out, **kw), None
+        return self.conv(name, x, out=out, out2=out2, slope2=slope2, **kw)
+
     # ---- video_net.py:74-96
     def res_block(self, pre, x, slope=0.01, start_from_relu=True, end_with_relu=False, out=None,
-                  res2=None):
+                  res2=None, x_act=None, twin_out=None, out2=None):
+        """x + conv2(act(conv1(act(x)))).  x_act: pre-activated twin of x (then conv1 needs no
+        pre-activation).  twin_out: slope of an activated twin of the result to emit as well
+        (returns (y, y_act))."""
         s = 0.0 if slope < 0.0001 else slope
-        t = self.conv(pre + ".conv1", x, pre=s if start_from_relu else None, post=s)
-        return self.conv(pre + ".conv2", t, post=s if end_with_relu else None, res=x, res2=res2, out=out)
+        if x_act is not None and start_from_relu:
+            t = self.conv(pre + ".conv1", x_act, post=s)
+        else:
+            t = self.conv(pre + ".conv1", x, pre=s if start_from_relu else None, post=s)
+        kw = dict(post=s if end_with_relu else None, res=x, res2=res2, out=out)
+        if twin_out is not None:
+            return self.conv_t(pre + ".conv2", t, twin_out, out2=out2, **kw)
+        return self.conv(pre + ".conv2", t, **kw)
 
     # ---- layers.py:42-73
     def residual_block_with_stride(self, pre, x):
@@ -93,10 +109,12 @@ class Graph:
         return self.conv(pre + ".4", x)
 
     # ---- video_net.py:149-179: up_dim(x) + conv(x) * se(conv(x))
-    def conv_block_residual(self, pre, x, out=None):
+    def conv_block_residual(self, pre, x, out=None, twin_out=None):
         t = self.conv(pre + ".conv.0", x, post=0.01)
         x1 = self.conv(pre + ".conv.2", t)
         s = self.B.se_scale(x1, self.lin(pre + ".conv.3.fc.0.weight"), self.lin(pre + ".conv.3.fc.2.weight"))
+        if twin_out is not None:
+            return self.conv_t(pre + ".up_dim", x, twin_out, res=x1, res_scale=s, out=out)
         return self.conv(pre + ".up_dim", x, res=x1, res_scale=s, out=out)
 
     # ---- video_net.py:182-223
@@ -107,9 +125,12 @@ class Graph:
         cat3 = B.new(N, H // 2, W // 2, 128, dtype=x.dtype)  # (x2 | d3)
         x1 = self.conv_block_residual(pre + ".conv1", x, out=cat2.sl(0, 32))
         x2 = self.conv_block_residual(pre + ".conv2", B.maxpool(x1), out=cat3.sl(0, 64))
-        x3 = self.conv_block_residual(pre + ".conv3", B.maxpool(x2))
+        x3, x3a = self.conv_block_residual(pre + ".conv3", B.maxpool(x2), twin_out=0.0)
         for i in range(4):
-            x3 = self.res_block(f"{pre}.context_refine.{i}", x3, slope=0)
+            if i < 3:
+                x3, x3a = self.res_block(f"{pre}.context_refine.{i}", x3, slope=0, x_act=x3a, twin_out=0.0)
+            else:
+                x3 = self.res_block(f"{pre}.context_refine.{i}", x3, slope=0, x_act=x3a)
         self.conv(pre + ".up3.0", x3, ps=True, out=cat3.sl(64, 128))
         d3 = self.conv_block_residual(pre + ".up_conv3", cat3)
         self.conv(pre + ".up2.0", d3, ps=True, out=cat2.sl(32, 64))
