@@ -1,0 +1,362 @@
+#!/usr/bin/env python
+"""bench.py -- 1080p DCVC-HEM encode+decode throughput (BASELINE.json metric) on N B200s.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--precision bf16|fp32] [--impl reference]
+
+One "step" = one synthetic GOP of `--gop` frames (1 I-frame through IntraNoAR + P-frames through
+DMC), 1920x1080 padded to 1920x1088, each frame going through the public
+`encode_decode`-equivalent call (compress -> real rANS bitstream -> decompress).  Every rank codes
+its own independent sequence (the path shards by sequence / GOP with no data-path collective), so
+scaling is "weak".  Two timed passes:
+
+  value : frames already resident in HBM, reconstruction left in HBM;
+  e2e   : frames start in pinned host memory (H2D inside the timed region) and every reconstructed
+          frame is copied back to pinned host memory (D2H inside the timed region).
+
+Both passes include the D2H of symbols/indexes, the CPU rANS coder and the H2D of decoded symbols:
+that hand-off is part of the path (the bitstream is produced and consumed on the host).
+Prints ONE JSON line (rank 0).  `--impl reference` times the CPU oracle port instead.
+"""
+import argparse
+import json
+import math
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+import torch  # noqa: E402
+
+H, W = 1080, 1920
+HP, WP = 1088, 1920
+METRIC = "1080p GOP encode+decode frames/sec"
+# algorithmic conv work per padded 1080p frame, FLOP
+P_FRAME_FLOP = 12.101e12
+I_FRAME_FLOP = 4.275e12
+
+
+def synth_sequence(n_frames, seed, device="cpu"):
+    """Smooth moving texture in [0,1] + 1 % noise, [n,3,1080,1920] fp32."""
+    g = torch.Generator(device="cpu").manual_seed(1234 + seed)
+    margin = 4 * n_frames + 16
+    ch, cw = (H + margin) // 16 + 2, (W + margin) // 16 + 2
+    coarse = torch.rand((1, 3, ch, cw), generator=g)
+    mid = torch.rand((1, 3, ch * 4, cw * 4), generator=g)
+    F = torch.nn.functional
+    base = 0.75 * F.interpolate(coarse, scale_factor=16, mode="bicubic", align_corners=False) + \
+        0.25 * F.interpolate(mid, scale_factor=4, mode="bicubic", align_corners=False)
+    base = base.clamp(0, 1)
+    out = torch.empty((n_frames, 3, H, W))
+    ox = oy = 0
+    for t in range(n_frames):
+        crop = base[0, :, oy:oy + H, ox:ox + W]
+        out[t] = (crop + 0.01 * torch.randn(crop.shape, generator=g)).clamp(0, 1)
+        ox += 1 + (t % 3)
+        oy += 1 + ((t + 1) % 2)
+    return out.to(device)
+
+
+def make_state_dicts(seed=0):
+    """Random-init weights of the reference architecture: its own init (xavier_normal gain sqrt 2,
+    bias 0.01) with conv weights x0.7 (un-scaled random init is numerically chaotic)."""
+    from vcm_ts_b200.models import DMC, IntraNoAR
+    torch.manual_seed(seed)
+    sds = []
+    for cls in (DMC, IntraNoAR):
+        m = cls()
+        sd = m.state_dict()
+        for k, v in sd.items():
+            if k.endswith(".weight") and v.dim() == 4:
+                v.mul_(0.7)
+        sds.append(sd)
+    return sds
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons during the timed region."""
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "200"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.25)
+        self.proc.terminate()
+        sm = sorted(int(r[0]) for r in self.rows if r and r[0].isdigit())
+        mx = [int(r[1]) for r in self.rows if len(r) > 1 and r[1].isdigit()]
+        names = ("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap")
+        reasons = [n for i, n in enumerate(names) if any(len(r) > 2 + i and r[2 + i] == "Active" for r in self.rows)]
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": reasons, "samples": len(sm)}
+
+
+def code_gop(dmc, intra, frames_src, gop, q, host_out=None, pinned_in=False, dev=None):
+    """Encode+decode one GOP.  frames_src[t]: [3,1080,1920] (device, or pinned host when pinned_in).
+    Returns (bits, last reconstruction)."""
+    F = torch.nn.functional
+    bits = 0
+    dpb = None
+    for t in range(gop):
+        fr = frames_src[t]
+        if pinned_in:
+            fr = fr.to(dev, non_blocking=True)
+        x = F.pad(fr[None], (0, WP - W, 0, HP - H))
+        if t == 0:
+            r, _ = intra.encode_decode_bytes(x, q, H, W)
+            rec = r["x_hat"]
+            dpb = {"ref_frame": rec, "ref_feature": None, "ref_y": None, "ref_mv_y": None}
+        else:
+            r, _ = dmc.encode_decode_bytes(x, dpb, H, W, q, q)
+            dpb = r["dpb"]
+            rec = dpb["ref_frame"]
+        bits += r["bit"]
+        if host_out is not None:
+            host_out[t].copy_(rec[0, :, :H, :W], non_blocking=True)
+    return bits, rec
+
+
+def conv_roofline(dmc, intra, x, dpb, q):
+    """Instrumented pass: CUDA events around every conv launch of one P-frame encode+decode, on the
+    launching stream.  Returns achieved TFLOP/s of the tcgen05 engine (algorithmic FLOPs / time)."""
+    B = dmc._rt.B
+    orig = B.conv
+    recs = []
+
+    def timed_conv(xv, pc, *a, **kw):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(torch.cuda.current_stream(B.device))
+        out = orig(xv, pc, *a, **kw)
+        e1.record(torch.cuda.current_stream(B.device))
+        stride = kw.get("stride", 1)
+        ho, wo = (xv.H + stride - 1) // stride, (xv.W + stride - 1) // stride
+        flop = 2.0 * xv.N * ho * wo * pc.K * pc.K * pc.Cin * pc.Cout
+        recs.append((e0, e1, flop, pc.w_umma is not None and xv.dtype == torch.bfloat16 and
+                     kw.get("pre") is None, (pc.K, stride, pc.Cin, pc.Cout, xv.H, xv.W)))
+        return out
+
+    B.conv = timed_conv
+    try:
+        dmc.encode_decode_bytes(x, dpb, H, W, q, q)
+        torch.cuda.synchronize()
+    finally:
+        B.conv = orig
+    tc_t = sum(e0.elapsed_time(e1) for e0, e1, _, tc, _ in recs if tc) * 1e-3
+    tc_f = sum(f for _, _, f, tc, _ in recs if tc)
+    all_t = sum(e0.elapsed_time(e1) for e0, e1, _, _, _ in recs) * 1e-3
+    all_f = sum(f for _, _, f, _, _ in recs)
+    by_shape = {}
+    for e0, e1, f, tc, shp in recs:
+        k = ("tc" if tc else "simt") + ":k%d s%d %d->%d @%dx%d" % shp
+        a = by_shape.setdefault(k, [0.0, 0.0, 0])
+        a[0] += e0.elapsed_time(e1)
+        a[1] += f
+        a[2] += 1
+    return dict(tc_s=tc_t, tc_flop=tc_f, all_s=all_t, all_flop=all_f, n=len(recs),
+                n_tc=sum(1 for r in recs if r[3]), by_shape=by_shape)
+
+
+def oracle_fps(sd_p, sd_i, threads, hh=544, ww=960, frames=1):
+    """CPU oracle port (reference algorithm, PyTorch CPU + C rANS) on a 960x544 crop: seconds per
+    P-frame encode+decode, converted to 1080p-equivalent frames/s by the pixel ratio (the nets are
+    fully convolutional, cost is linear in pixels)."""
+    from oracle import dcvc_oracle as O
+    torch.set_num_threads(threads)
+    odmc, ointra = O.OracleDMC(sd_p), O.OracleIntra(sd_i)
+    odmc.update()
+    ointra.update()
+    seq = synth_sequence(frames + 1, 0)[:, :, :hh, :ww].contiguous()
+    t0 = time.time()
+    r, _ = ointra.encode_decode_bytes(seq[0:1], 1.0, hh, ww)
+    t_i = time.time() - t0
+    dpb = {"ref_frame": r["x_hat"], "ref_feature": None, "ref_y": None, "ref_mv_y": None}
+    t0 = time.time()
+    for t in range(1, frames + 1):
+        r, _ = odmc.encode_decode_bytes(seq[t:t + 1], dpb, hh, ww, 1.0, 1.0)
+        dpb = r["dpb"]
+    t_p = (time.time() - t0) / frames
+    ratio = (HP * WP) / float(hh * ww)
+    return dict(p_frame_s_1080p=t_p * ratio, i_frame_s_1080p=t_i * ratio,
+                sample=f"{frames} P-frame(s) + 1 I-frame encode+decode at {ww}x{hh}, scaled x{ratio:.2f} to 1080p")
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=2)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--gop", type=int, default=32)
+    ap.add_argument("--precision", default=os.environ.get("VCM_B200_PRECISION", "bf16"))
+    ap.add_argument("--impl", default="b200")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    a = ap.parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    gop = a.gop
+    cfg = {"workload": f"DCVC-HEM GOP-{gop} 1080p (1920x1088 padded) sequence encode+decode per GPU: "
+                       f"1 I-frame (IntraNoAR) + {gop - 1} P-frames (DMC), real rANS bitstreams",
+           "gop": gop, "sequences_per_gpu": 1, "precision": a.precision, "parallelism": f"seq-shard x{world}",
+           "weights": "random init (reference init, conv x0.7)",
+           "l2": "working set per frame >> 126 MB L2 (1080p activations), no explicit flush"}
+    sd_p, sd_i = make_state_dicts(0)
+
+    if a.impl == "reference":
+        if rank != 0:
+            return
+        threads = os.cpu_count() or 1
+        vals = []
+        for _ in range(a.warmup if a.warmup < 1 else 0):
+            oracle_fps(sd_p, sd_i, threads)
+        t_all = []
+        last = None
+        for _ in range(max(1, a.steps)):
+            t0 = time.time()
+            last = oracle_fps(sd_p, sd_i, threads)
+            t_all.append(time.time() - t0)
+            per_gop = last["i_frame_s_1080p"] + (gop - 1) * last["p_frame_s_1080p"]
+            vals.append(gop / per_gop)
+        v = sum(vals) / len(vals)
+        print(json.dumps({
+            "impl": "reference", "metric": METRIC, "value": v, "unit": "frames/s", "n_gpus": a.gpus,
+            "steps": a.steps, "warmup": a.warmup, "ms_per_step": 1e3 * sum(t_all) / len(t_all),
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+            "data": "synthetic", "config": cfg,
+            "cpu_baseline": {"value": v, "unit": "frames/s", "cores": threads, "kind": "port",
+                             "sample": last["sample"] + "; GOP value = gop / (I + (gop-1) P)"},
+            "e2e": {"value": v, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}))
+        return
+
+    import torch.distributed as dist
+    if world > 1:
+        dist.init_process_group("nccl", init_method="env://", device_id=torch.device(f"cuda:{local}"))
+    dev = torch.device(f"cuda:{local}")
+    torch.cuda.set_device(dev)
+    from vcm_ts_b200.models import DMC, IntraNoAR
+    dmc, intra = DMC(precision=a.precision).eval(), IntraNoAR(precision=a.precision).eval()
+    dmc.load_state_dict(sd_p)
+    intra.load_state_dict(sd_i)
+    dmc, intra = dmc.to(dev), intra.to(dev)
+    dmc.update(force=True)
+    intra.update(force=True)
+    q = 1.0
+    seq_host = synth_sequence(gop, rank).pin_memory()
+    seq_dev = seq_host.to(dev)
+    host_out = torch.empty((gop, 3, H, W), dtype=torch.float32).pin_memory()
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, steps):
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(steps):
+            fn()
+        e1.record()
+        barrier()
+        ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
+        if world > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        return ms.item()
+
+    bits_box = [0]
+
+    def step_resident():
+        bits_box[0], _ = code_gop(dmc, intra, seq_dev, gop, q)
+
+    def step_e2e():
+        bits_box[0], _ = code_gop(dmc, intra, seq_host, gop, q, host_out=host_out, pinned_in=True, dev=dev)
+        torch.cuda.synchronize()
+
+    # warm-up (>= 3 coded frames each through both models; W steps of a short GOP)
+    for _ in range(max(a.warmup, 1)):
+        code_gop(dmc, intra, seq_dev, min(gop, 3), q)
+    B = dmc._rt.B
+    Bi = intra._rt.B
+    clocks = ClockSampler(local)
+    clocks.start()
+    l0 = B.launches + Bi.launches
+    ms_res = timed(step_resident, a.steps)
+    launches = B.launches + Bi.launches - l0
+    ms_e2e = timed(step_e2e, a.steps)
+    clk = clocks.stop()
+    frames_total = gop * a.steps * world
+    value = frames_total / (ms_res * 1e-3)
+    e2e = frames_total / (ms_e2e * 1e-3)
+    bpp = bits_box[0] / float(gop * H * W)
+
+    roof = None
+    cpu = None
+    if rank == 0:
+        F = torch.nn.functional
+        x1 = F.pad(seq_dev[1:2], (0, WP - W, 0, HP - H))
+        x0 = F.pad(seq_dev[0:1], (0, WP - W, 0, HP - H))
+        r0, _ = intra.encode_decode_bytes(x0, q, H, W)
+        dpb = {"ref_frame": r0["x_hat"], "ref_feature": None, "ref_y": None, "ref_mv_y": None}
+        rf = conv_roofline(dmc, intra, x1, dpb, q)
+        peaks = {}
+        try:
+            peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        except Exception:
+            pass
+        peak = peaks.get("bf16_tflops_sustained", 1400.0)
+        use_tc = rf["tc_s"] > 0
+        ach = (rf["tc_flop"] / rf["tc_s"] if use_tc else rf["all_flop"] / max(rf["all_s"], 1e-9)) / 1e12
+        roof = {"bound": "tensor", "kernel": "conv_tc_kernel (tcgen05 implicit GEMM)" if use_tc else "conv_simt_kernel",
+                "achieved": ach, "peak": peak, "unit": "TFLOP/s", "frac": ach / peak,
+                "peak_source": "MEASURED_PEAKS.json bf16_tflops_sustained" if peaks else "fallback 1400 (sustained)",
+                "traffic": None,
+                "launches_timed": rf["n_tc"] if use_tc else rf["n"],
+                "conv_share_of_p_frame": {"tc_ms": rf["tc_s"] * 1e3, "all_conv_ms": rf["all_s"] * 1e3,
+                                          "all_conv_tflops": rf["all_flop"] / max(rf["all_s"], 1e-9) / 1e12}}
+        os.makedirs(os.path.join(ROOT, "gpurun_out"), exist_ok=True)
+        with open(os.path.join(ROOT, "gpurun_out", f"conv_by_shape_{a.precision}.json"), "w") as f:
+            top = sorted(rf["by_shape"].items(), key=lambda kv: -kv[1][0])
+            json.dump([{"shape": k, "ms": v[0], "tflops": v[1] / max(v[0], 1e-9) / 1e9, "calls": v[2]}
+                       for k, v in top], f, indent=1)
+        if not a.no_cpu_baseline:
+            threads = os.cpu_count() or 1
+            ob = oracle_fps(sd_p, sd_i, threads)
+            per_gop = ob["i_frame_s_1080p"] + (gop - 1) * ob["p_frame_s_1080p"]
+            cpu = {"value": gop / per_gop, "unit": "frames/s", "cores": threads, "kind": "port",
+                   "sample": ob["sample"]}
+    if rank == 0:
+        seq_bytes = gop * 3 * H * W * 4
+        print(json.dumps({
+            "metric": METRIC, "value": value, "unit": "frames/s", "n_gpus": world, "steps": a.steps,
+            "warmup": a.warmup, "ms_per_step": ms_res / a.steps, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "bf16" if a.precision == "bf16" else "f32", "data": "synthetic",
+            "config": cfg, "clocks": clk, "bpp": bpp,
+            "e2e": {"value": e2e, "unit": "frames/s", "h2d_bytes_per_step": seq_bytes,
+                    "d2h_bytes_per_step": seq_bytes, "ms_per_step": ms_e2e / a.steps},
+            "gpu_launches": launches, "roofline": roof, "cpu_baseline": cpu}))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

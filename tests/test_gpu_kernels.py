@@ -1,0 +1,377 @@
+"""`-m gpu` kernel-level parity tests: every C-ABI kernel of libvcmts_b200.so against the op of the
+reference it replaces, evaluated with stock torch ops / the oracle on the same seeded inputs.
+
+Integer outputs (symbols, scale indexes) are compared bit-exactly; fp32 kernels within a few ulp
+(stated per test); the tcgen05 bf16 engine against an fp32 convolution of the same bf16-rounded
+operands (only accumulation order and the final bf16 rounding differ).
+"""
+import json
+import os
+
+import numpy as np
+import pytest
+import torch
+import torch.nn.functional as F
+
+pytestmark = pytest.mark.gpu
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+@pytest.fixture(scope="module")
+def B32():
+    from vcm_ts_b200.backend import CudaBackend
+    torch.backends.cudnn.allow_tf32 = False
+    torch.backends.cuda.matmul.allow_tf32 = False
+    return CudaBackend("cuda:0", "fp32")
+
+
+@pytest.fixture(scope="module")
+def B16():
+    from vcm_ts_b200.backend import CudaBackend
+    return CudaBackend("cuda:0", "bf16")
+
+
+def view_of(t_nchw, dtype=torch.float32, cs=None, c0=0):
+    """NCHW tensor -> View (optionally a channel slice of a wider NaN-free buffer)."""
+    from vcm_ts_b200.backend import View
+    N, C, H, W = t_nchw.shape
+    cs = cs or C
+    buf = torch.zeros((N, H, W, cs), dtype=dtype, device=t_nchw.device)
+    buf[..., c0:c0 + C] = t_nchw.permute(0, 2, 3, 1).to(dtype)
+    return View(buf, c0, C)
+
+
+def nchw(v):
+    return v.dense().permute(0, 3, 1, 2).float().contiguous()
+
+
+def ref_conv(x, w, b, stride, pre, post, ps, res, res_scale, res2):
+    t = x if pre is None else F.leaky_relu(x, pre)
+    y = F.conv2d(t, w, b, stride, w.shape[-1] // 2)
+    if post is not None:
+        y = F.leaky_relu(y, post)
+    if ps:
+        y = F.pixel_shuffle(y, 2)
+    if res is not None and res_scale is None:
+        y = res + y
+    if res is not None and res_scale is not None:
+        y = y + res * res_scale[:, :, None, None]
+    if res2 is not None:
+        y = res2 + y
+    return y
+
+
+CONV_CASES = [
+    # K, stride, Cin, Cout, H, W, N, pre, post, ps, res, res_scale, res2, slope2
+    (3, 1, 64, 64, 40, 56, 1, None, None, False, False, False, False, None),
+    (3, 1, 64, 64, 33, 47, 2, 0.01, 0.01, False, True, False, True, 0.1),
+    (3, 2, 67, 64, 32, 48, 1, None, 0.1, False, False, False, False, None),
+    (7, 1, 8, 32, 24, 40, 1, None, 0.0, False, False, False, False, None),
+    (7, 1, 16, 2, 24, 40, 1, None, None, False, True, False, False, None),
+    (1, 1, 64, 256, 17, 30, 1, None, 0.01, True, False, False, False, None),
+    (1, 2, 2, 64, 32, 48, 1, None, None, False, False, False, False, None),
+    (1, 1, 32, 64, 16, 24, 2, None, None, False, True, True, False, 0.0),
+    (3, 1, 128, 256, 16, 24, 1, None, None, True, True, False, False, 0.01),
+    (3, 2, 3, 192, 64, 64, 1, None, None, False, False, False, False, None),
+]
+
+
+@pytest.mark.parametrize("case", CONV_CASES)
+def test_conv_fp32_engine(B32, case):
+    K, stride, Cin, Cout, H, W, N, pre, post, ps, use_res, use_scale, use_res2, slope2 = case
+    g = torch.Generator(device="cpu").manual_seed(CONV_CASES.index(case))
+    dev = "cuda:0"
+    x = torch.randn((N, Cin, H, W), generator=g).to(dev)
+    w = (torch.randn((Cout, Cin, K, K), generator=g) / (Cin * K * K) ** 0.5).to(dev)
+    b = torch.randn((Cout,), generator=g).to(dev)
+    Ho, Wo = (H + 2 * (K // 2) - K) // stride + 1, (W + 2 * (K // 2) - K) // stride + 1
+    oshape = (N, Cout // 4, 2 * Ho, 2 * Wo) if ps else (N, Cout, Ho, Wo)
+    res = torch.randn(oshape, generator=g).to(dev) if use_res else None
+    res2 = torch.randn(oshape, generator=g).to(dev) if use_res2 else None
+    scale = torch.rand((N, oshape[1]), generator=g).to(dev).contiguous() if use_scale else None
+    pc = B32.pack_conv(w, b)
+    xv = view_of(x, cs=Cin + 5, c0=3) if Cin % 4 else view_of(x, cs=Cin + 8, c0=4)
+    out = B32.conv(xv, pc, stride=stride, pre=pre, post=post, ps=ps,
+                   res=view_of(res, cs=oshape[1] + 4, c0=4) if use_res else None, res_scale=scale,
+                   res2=view_of(res2) if use_res2 else None, slope2=slope2)
+    out2 = None
+    if slope2 is not None:
+        out, out2 = out
+    want = ref_conv(x, w, b, stride, pre, post, ps, res, scale, res2)
+    got = nchw(out)
+    torch.testing.assert_close(got, want, rtol=2e-5, atol=2e-5)
+    if out2 is not None:
+        torch.testing.assert_close(nchw(out2), F.leaky_relu(want, slope2), rtol=2e-5, atol=2e-5)
+
+
+def test_conv_mixed_dtypes(B32):
+    """fp32 in -> bf16 out and bf16 in -> fp32 out (the flow / frame boundaries of bf16 mode)."""
+    dev = "cuda:0"
+    g = torch.Generator().manual_seed(3)
+    x = torch.randn((1, 8, 20, 28), generator=g).to(dev)
+    w = (torch.randn((32, 8, 7, 7), generator=g) / 20).to(dev)
+    b = torch.randn((32,), generator=g).to(dev)
+    pc = B32.pack_conv(w, b)
+    y = B32.conv(view_of(x), pc, post=0.0, out_dtype=torch.bfloat16)
+    want = F.relu(F.conv2d(x, w, b, 1, 3))
+    torch.testing.assert_close(nchw(y), want.bfloat16().float(), rtol=1e-2, atol=1e-2)
+    xb = view_of(want, dtype=torch.bfloat16)
+    w2 = (torch.randn((2, 32, 7, 7), generator=g) / 40).to(dev)
+    b2 = torch.randn((2,), generator=g).to(dev)
+    r = torch.randn((1, 2, 20, 28), generator=g).to(dev)
+    y2 = B32.conv(xb, B32.pack_conv(w2, b2), res=view_of(r), out_dtype=torch.float32)
+    want2 = r + F.conv2d(nchw(xb), w2, b2, 1, 3)
+    torch.testing.assert_close(nchw(y2), want2, rtol=1e-4, atol=1e-4)
+
+
+def test_umma_descriptor_probe(B16):
+    """Records how the tensor core addresses a 128B-swizzled A tile that starts a few rows into the
+    buffer / whose 8-row groups are 1280 B apart (what a halo-tile implicit GEMM needs).  Only the
+    canonical case is asserted; the table goes to gpurun_out/umma_probe.json."""
+    L = B16.L
+    out = torch.zeros((128, 64), dtype=torch.float32, device="cuda:0")
+    table = {}
+    for start_row in (0, 1, 3, 8, 11):
+        for sbo in (1024, 1280, 2048):
+            for use_bo in (0, 1):
+                out.zero_()
+                rc = L.vcm_umma_probe(start_row, sbo, use_bo, out.data_ptr(), B16.stream)
+                assert rc == 0, L.vcm_last_error()
+                torch.cuda.synchronize()
+                m = torch.arange(128)
+                rows = start_row + (m // 8) * (sbo // 128) + m % 8
+                want = ((rows[:, None] * 64 + torch.arange(64)[None, :]) % 251).float()
+                ok = bool(torch.equal(out.cpu(), want))
+                table[f"start{start_row}_sbo{sbo}_bo{use_bo}"] = ok
+    os.makedirs(os.path.join(ROOT, "gpurun_out"), exist_ok=True)
+    with open(os.path.join(ROOT, "gpurun_out", "umma_probe.json"), "w") as f:
+        json.dump(table, f, indent=1)
+    print(table)
+    assert table["start0_sbo1024_bo0"], "canonical SW128 K-major descriptor does not work"
+
+
+TC_CASES = [
+    # K, stride, Cin, Cout, H, W, N, post, ps, res, res_scale, res2, slope2
+    (3, 1, 64, 64, 40, 56, 1, None, False, False, False, False, None),
+    (3, 1, 64, 64, 64, 96, 2, 0.01, False, True, False, True, 0.1),
+    (3, 1, 128, 64, 24, 48, 1, 0.2, False, False, False, False, None),
+    (3, 1, 96, 64, 17, 30, 1, None, False, False, False, False, None),
+    (3, 1, 144, 192, 17, 30, 1, 0.01, False, False, False, False, None),
+    (7, 1, 32, 64, 32, 48, 1, 0.0, False, False, False, False, None),
+    (7, 1, 64, 32, 32, 48, 1, 0.0, False, False, False, False, None),
+    (7, 1, 32, 16, 16, 32, 1, 0.0, False, False, False, False, None),
+    (1, 1, 64, 256, 17, 30, 1, 0.01, True, False, False, False, None),
+    (3, 1, 64, 256, 16, 32, 1, None, True, True, False, False, 0.01),
+    (1, 1, 64, 32, 32, 32, 1, None, False, True, True, False, 0.0),
+    (3, 1, 480, 384, 17, 30, 1, 0.2, False, False, False, False, None),
+    (3, 2, 64, 64, 32, 64, 1, 0.01, False, False, False, False, 0.01),
+    (3, 2, 128, 64, 48, 32, 2, None, False, False, False, False, None),
+    (1, 2, 64, 64, 32, 32, 1, None, False, False, False, False, None),
+]
+
+
+@pytest.mark.parametrize("case", TC_CASES)
+def test_conv_tcgen05_engine(B16, case):
+    K, stride, Cin, Cout, H, W, N, post, ps, use_res, use_scale, use_res2, slope2 = case
+    import ctypes
+    from vcm_ts_b200 import _lib
+    g = torch.Generator(device="cpu").manual_seed(100 + TC_CASES.index(case))
+    dev = "cuda:0"
+    bf = torch.bfloat16
+    x = torch.randn((N, Cin, H, W), generator=g).to(dev).to(bf)
+    w = (torch.randn((Cout, Cin, K, K), generator=g) / (Cin * K * K) ** 0.5).to(dev)
+    b = torch.randn((Cout,), generator=g).to(dev)
+    Ho, Wo = (H + 2 * (K // 2) - K) // stride + 1, (W + 2 * (K // 2) - K) // stride + 1
+    oshape = (N, Cout // 4, 2 * Ho, 2 * Wo) if ps else (N, Cout, Ho, Wo)
+    res = torch.randn(oshape, generator=g).to(dev).to(bf) if use_res else None
+    res2 = torch.randn(oshape, generator=g).to(dev).to(bf) if use_res2 else None
+    scale = torch.rand((N, oshape[1]), generator=g).to(dev).contiguous() if use_scale else None
+    pc = B16.pack_conv(w, b)
+    assert pc.w_umma is not None
+    xv = view_of(x.float(), dtype=bf, cs=Cin + 16, c0=8)
+    rv = view_of(res.float(), dtype=bf, cs=oshape[1] + 8, c0=8) if use_res else None
+    d = _lib.ConvDesc(N, H, W, Cin, Cout, K, stride, xv.cs, oshape[1], rv.cs if rv else 0,
+                      oshape[1] if use_res2 else 0, oshape[1], 0, 0.0, 0.0, 0.0, _lib.BF16, _lib.BF16)
+    assert B16.L.vcm_conv2d_tc_supported(ctypes.byref(d)) == 1, "case must exercise the tcgen05 engine"
+    out = B16.conv(xv, pc, stride=stride, post=post, ps=ps, res=rv, res_scale=scale,
+                   res2=view_of(res2.float(), dtype=bf) if use_res2 else None, slope2=slope2)
+    out2 = None
+    if slope2 is not None:
+        out, out2 = out
+    torch.cuda.synchronize()
+    want = ref_conv(x.float(), w.to(bf).float(), b, stride, None, post, ps,
+                    res.float() if use_res else None, scale, res2.float() if use_res2 else None)
+    got = nchw(out)
+    err = (got - want).abs()
+    tol = 0.01 * want.abs() + 0.02
+    assert bool((err <= tol).all()), f"max err {err.max().item():.4f} (rms of want {want.pow(2).mean().sqrt().item():.3f})"
+    if out2 is not None:
+        w2 = F.leaky_relu(want, slope2)
+        assert bool(((nchw(out2) - w2).abs() <= 0.01 * w2.abs() + 0.02).all())
+
+
+def test_layout_and_pool_kernels(B32):
+    dev = "cuda:0"
+    g = torch.Generator().manual_seed(0)
+    x = torch.randn((2, 37, 18, 26), generator=g).to(dev)
+    v = B32.from_nchw(x)
+    assert torch.equal(nchw(v), x)
+    assert torch.equal(B32.to_nchw(v), x)
+    assert torch.equal(B32.to_nchw(v, clamp=(0.0, 1.0)), x.clamp(0, 1))
+    vb = B32.from_nchw(x, dtype=torch.bfloat16)
+    assert torch.equal(nchw(vb), x.bfloat16().float())
+    assert torch.equal(nchw(B32.maxpool(v)), F.max_pool2d(x, 2, 2))
+    x3 = torch.rand((2, 3, 32, 48), generator=g).to(dev)
+    torch.testing.assert_close(nchw(B32.avgpool(view_of(x3, cs=8))), F.avg_pool2d(x3, 2, 2), rtol=0, atol=1e-7)
+    vec = (torch.rand((2, 37), generator=g) + 0.5).to(dev).contiguous()
+    assert torch.equal(nchw(B32.scale(v, vec, "div")), x / vec[:, :, None, None])
+    assert torch.equal(nchw(B32.scale(v, vec, "mul")), x * vec[:, :, None, None])
+    dst = view_of(torch.zeros((2, 37, 18, 26), device=dev), cs=64, c0=16)
+    B32.copy(v, dst)
+    assert torch.equal(nchw(dst), x)
+
+
+def test_se_layer(B32):
+    dev = "cuda:0"
+    g = torch.Generator().manual_seed(1)
+    for C, H, W in ((32, 64, 96), (128, 70, 90), (64, 16, 16)):
+        x = torch.randn((2, C, H, W), generator=g).to(dev)
+        w1 = (torch.randn((C // 16, C), generator=g) / C ** 0.5).to(dev).contiguous()
+        w2 = (torch.randn((C, C // 16), generator=g)).to(dev).contiguous()
+        want = torch.sigmoid(F.linear(F.relu(F.linear(x.mean(dim=(-1, -2)), w1)), w2))
+        got = B32.se_scale(view_of(x), w1, w2)
+        torch.testing.assert_close(got, want, rtol=1e-5, atol=1e-6)
+        got2 = B32.se_scale(view_of(x), w1, w2)
+        assert torch.equal(got, got2), "SE reduction must be deterministic"
+
+
+def test_motion_kernels(B32):
+    from oracle import dcvc_oracle as O
+    dev = "cuda:0"
+    g = torch.Generator().manual_seed(2)
+    flow = (torch.randn((2, 2, 17, 30), generator=g) * 3).to(dev)
+    up = B32.flow_up2(view_of(flow), gain=2.0)
+    torch.testing.assert_close(nchw(up), O.bilinear_up2(flow) * 2.0, rtol=0, atol=1e-6)
+    big = (torch.randn((1, 2, 64, 96), generator=g) * 4).to(dev)
+    dn = B32.flow_down2(view_of(big), gain=0.5)
+    torch.testing.assert_close(nchw(dn), O.bilinear_down2(big) / 2, rtol=0, atol=1e-6)
+    for C, dt in ((3, torch.float32), (64, torch.float32), (64, torch.bfloat16)):
+        feat = torch.randn((1, C, 64, 96), generator=g).to(dev)
+        fl = big.clone()
+        fl[:, :, :4] *= 20          # drive samples out of the image: border clamp
+        want = O.torch_warp(feat.cpu(), fl.cpu()).to(dev) if dt == torch.float32 else \
+            O.torch_warp(feat.bfloat16().float().cpu(), fl.cpu()).to(dev)
+        got = B32.warp(view_of(feat, dtype=dt, cs=C + (8 if C > 3 else 5)),
+                       view_of(fl))
+        if dt == torch.float32:
+            torch.testing.assert_close(nchw(got), want, rtol=0, atol=2e-4)
+        else:
+            torch.testing.assert_close(nchw(got), want, rtol=1e-2, atol=2e-2)
+
+
+def _dp_inputs(C, h, w, seed):
+    g = torch.Generator().manual_seed(seed)
+    y = torch.randn((1, C, h, w), generator=g) * 3
+    q_step = torch.rand((1, C, h, w), generator=g) * 1.5 + 0.1
+    scales = torch.randn((1, C, h, w), generator=g).abs() * 2 - 0.2      # some <= 0
+    means = torch.randn((1, C, h, w), generator=g)
+    prior = torch.randn((1, 2 * C, h, w), generator=g)
+    prior[:, :C // 2] = prior[:, :C // 2].abs() * 3
+    prior[:, C:C + C // 2] = prior[:, C:C + C // 2].abs() * 0.05
+    q_outer = torch.rand((1, C), generator=g) + 0.5
+    return y, q_step, scales, means, prior, q_outer
+
+
+@pytest.mark.parametrize("dist,C,h,w", [("laplace", 64, 17, 30), ("laplace", 96, 12, 20), ("gaussian", 192, 8, 14)])
+def test_dual_prior_kernels_bit_exact(B32, dist, C, h, w):
+    """Teacher-forced: identical float inputs -> symbols, scale indexes and y_hat must equal
+    common_model.py:104-217 exactly (oracle restatement), encode and decode sides."""
+    from oracle import dcvc_oracle as O
+    from vcm_ts_b200.entropy import ScaleIndexTable
+    dev = "cuda:0"
+    y, q_step, scales, means, prior_out, q_outer = _dp_inputs(C, h, w, 5)
+    table = ScaleIndexTable(dist)
+    otab = O.ScaleTable(dist)
+    # oracle: forward_dual_prior with the spatial prior replaced by a fixed tensor
+    m0, m1 = O.checkerboard(h, w)
+    qs = O.lower_bound(q_step, 0.5)
+    yq = y / qs
+    y0, y1 = yq.chunk(2, 1)
+    s0, s1 = scales.chunk(2, 1)
+    u0, u1 = means.chunk(2, 1)
+    _, q00, h00, sh00 = O._masked(y0, s0, u0, m0)
+    _, q11, h11, sh11 = O._masked(y1, s1, u1, m1)
+    ps0, pu0, ps1, pu1 = prior_out.chunk(4, 1)
+    _, q01, h01, sh01 = O._masked(y0, ps0, pu0, m1)
+    _, q10, h10, sh10 = O._masked(y1, ps1, pu1, m0)
+    want_yhat = torch.cat((h00 + h01, h11 + h10), 1) * qs * q_outer[:, :, None, None]
+    want = dict(sym0=(q00 + q11).to(torch.int16), sym1=(q01 + q10).to(torch.int16),
+                idx0=otab.build_indexes(sh00 + sh11).to(torch.uint8),
+                idx1=otab.build_indexes(sh01 + sh10).to(torch.uint8))
+    fusion = view_of(torch.cat((q_step, scales, means), 1).to(dev))
+    prior = view_of(prior_out.to(dev))
+    yv = view_of(y.to(dev))
+    qo = q_outer.to(dev).contiguous()
+    params = B32.new(1, h, w, 4 * C)
+    yqb = B32.empty((1, h, w, C), torch.float32)
+    plane = (1, C // 2, h, w)
+    sym0, sym1 = B32.empty(plane, torch.int16), B32.empty(plane, torch.int16)
+    idx0, idx1 = B32.empty(plane, torch.uint8), B32.empty(plane, torch.uint8)
+    yqf, scf = B32.empty((1, h, w, C), torch.float32), B32.empty((1, h, w, C), torch.float32)
+    B32.dp_pass0(0, table, fusion, params, C, y=yv, yq=yqb, sym=sym0, idx=idx0, y_q_full=yqf, scales_full=scf)
+    want_params = torch.cat((h00, h11, means, scales, qs), 1)
+    assert torch.equal(nchw(params).cpu(), want_params)
+    y_hat = B32.new(1, h, w, C)
+    B32.dp_pass1(0, table, fusion, prior, params, C, q_outer=qo, y_hat=y_hat, yq=yqb, sym=sym1, idx=idx1,
+                 y_q_full=yqf, scales_full=scf)
+    assert torch.equal(sym0.cpu(), want["sym0"]) and torch.equal(sym1.cpu(), want["sym1"])
+    assert torch.equal(idx0.cpu(), want["idx0"]) and torch.equal(idx1.cpu(), want["idx1"])
+    assert torch.equal(nchw(y_hat).cpu(), want_yhat)
+    assert torch.equal(yqf.permute(0, 3, 1, 2).cpu(), torch.cat((q00 + q01, q11 + q10), 1))
+    assert torch.equal(scf.permute(0, 3, 1, 2).cpu(), torch.cat((sh00 + sh01, sh11 + sh10), 1))
+    # decoder side: index-only passes give the same indexes, reconstruct passes the same y_hat
+    params2 = B32.new(1, h, w, 4 * C)
+    i0 = B32.empty(plane, torch.uint8)
+    B32.dp_pass0(1, table, fusion, params2, C, idx=i0)
+    assert torch.equal(i0, idx0)
+    B32.dp_pass0(2, table, fusion, params2, C, sym=sym0)
+    assert torch.equal(params2.dense(), params.dense())
+    i1 = B32.empty(plane, torch.uint8)
+    B32.dp_pass1(1, table, fusion, prior, params2, C, idx=i1)
+    assert torch.equal(i1, idx1)
+    y_hat2 = B32.new(1, h, w, C)
+    B32.dp_pass1(2, table, fusion, prior, params2, C, q_outer=qo, y_hat=y_hat2, sym=sym1)
+    assert torch.equal(y_hat2.dense(), y_hat.dense())
+
+
+def test_round_and_bits_kernels(B32):
+    from oracle import dcvc_oracle as O
+    from oracle import fixture
+    dev = "cuda:0"
+    g = torch.Generator().manual_seed(9)
+    z = torch.randn((2, 64, 9, 14), generator=g) * 4
+    z[0, 0, 0, :4] = torch.tensor([0.5, 1.5, -0.5, 2.5])          # round-half-to-even
+    sym = B32.empty((2, 64, 9, 14), torch.int16)
+    zh = B32.round_latent(view_of(z.to(dev)), sym=sym)
+    assert torch.equal(nchw(zh).cpu(), torch.round(z)) and torch.equal(sym.cpu(), torch.round(z).to(torch.int16))
+    back = B32.symbols_to_latent(sym, 2, 9, 14, 64)
+    assert torch.equal(nchw(back).cpu(), torch.round(z))
+    # likelihood kernels vs the oracle's restatement of common_model.py:51-73
+    yq = torch.round(torch.randn((2, 9, 14, 96), generator=g) * 3)
+    sc = torch.randn((2, 9, 14, 96), generator=g).abs() * 2
+    for dist, fn in (("laplace", O.laplace_bits), ("gaussian", O.gaussian_bits)):
+        want = fn(yq, sc).reshape(2, -1).sum(1)
+        got = B32.latent_bits(yq.to(dev).contiguous(), sc.to(dev).contiguous(), 2, dist)
+        torch.testing.assert_close(got.cpu(), want, rtol=2e-5, atol=1e-3)
+    P = fixture.fixture_state_dict({k: s for k, s in O.state_shapes("dmc").items() if k.startswith("bit_estimator_z.")})
+    rows = [P[f"bit_estimator_z.{f}.{p}"].reshape(-1) for f in ("f1", "f2", "f3", "f4") for p in ("h", "b", "a")
+            if not (f == "f4" and p == "a")]
+    fparams = torch.stack(rows).to(dev).contiguous()
+    zr = torch.round(z)
+    want = O.z_bits(P, "bit_estimator_z", zr).reshape(2, -1).sum(1)
+    got = B32.factorized_bits(view_of(zr.to(dev)), fparams)
+    torch.testing.assert_close(got.cpu(), want, rtol=2e-5, atol=1e-3)
+    a, b = torch.rand((2, 3, 40, 50), generator=g), torch.rand((2, 3, 40, 50), generator=g)
+    torch.testing.assert_close(B32.sq_err_sum(a.to(dev), b.to(dev)).cpu(), ((a - b) ** 2).reshape(2, -1).sum(1),
+                               rtol=1e-5, atol=1e-5)
