@@ -1,0 +1,84 @@
+// vcm_ts_b200/csrc/tc_probe.cu -- probe of the UMMA shared-memory descriptor semantics (see
+// include/vcmts_b200.h vcm_umma_probe): measured on B200, the 128B swizzle is a function of the
+// absolute shared-memory address, so an A tile may start any number of 128-byte rows into a
+// TMA-written buffer and use any multiple of 128 B as the stride between 8-row groups, with
+// base_offset = 0 (profiles/umma_probe_r01.json).  The halo-tile conv variant relies on this.
+#include "tc_ptx.cuh"
+using namespace tc;
+
+namespace {
+// ---------------------------------------------------------------------------------- probe
+// One 128 x 64 x 64 MMA with an identity B: D[m][n] = A[row(m)][n], where the tensor core fetches
+// row(m) from a 128B-swizzled buffer starting `start_row` rows in, 8-row groups `sbo` bytes apart.
+__global__ void __launch_bounds__(128, 1) umma_probe_kernel(int start_row, int sbo_bytes, int use_base_offset,
+                                                            float* __restrict__ out) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  constexpr int A_ROWS = 320;
+  uint8_t* sA = smem;                      // A_ROWS x 128 B
+  uint8_t* sB = smem + A_ROWS * 128;       // 64 x 128 B
+  uint64_t* bar = reinterpret_cast<uint64_t*>(sB + 64 * 128);
+  uint32_t* slot = reinterpret_cast<uint32_t*>(bar + 1);
+  for (int i = threadIdx.x; i < A_ROWS * 64; i += blockDim.x) {
+    const int p = i / 64, c = i % 64;
+    const uint32_t off = p * 128 + (((c >> 3) ^ (p & 7)) << 4) + (c & 7) * 2;
+    *reinterpret_cast<__nv_bfloat16*>(sA + off) = __float2bfloat16_rn((float)((p * 64 + c) % 251));
+  }
+  for (int i = threadIdx.x; i < 64 * 64; i += blockDim.x) {
+    const int nrow = i / 64, k = i % 64;
+    const uint32_t off = nrow * 128 + (((k >> 3) ^ (nrow & 7)) << 4) + (k & 7) * 2;
+    *reinterpret_cast<__nv_bfloat16*>(sB + off) = __float2bfloat16_rn(nrow == k ? 1.f : 0.f);
+  }
+  if (threadIdx.x == 0) {
+    mbar_init(bar, 1);
+    fence_barrier_init();
+  }
+  fence_proxy_async();
+  if ((threadIdx.x >> 5) == 0) tmem_alloc(slot, 64);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *slot;
+  if (threadIdx.x == 0) {
+    const uint32_t a0 = smem_u32(sA) + (uint32_t)start_row * 128u;
+    const uint32_t bo = use_base_offset ? ((a0 >> 7) & 7u) : 0u;
+    const uint64_t adesc = make_smem_desc(a0, (uint32_t)sbo_bytes, 2u, bo);
+    const uint64_t bdesc = make_smem_desc(smem_u32(sB), 1024u, 2u);
+    const uint32_t idesc = make_idesc_bf16(128, 64);
+#pragma unroll
+    for (int k = 0; k < 4; ++k) umma_bf16(tmem_base, adesc + (uint64_t)(2 * k), bdesc + (uint64_t)(2 * k), idesc, k > 0);
+    umma_commit(bar);
+  }
+  mbar_wait(bar, 0);
+  tc_fence_after();
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  for (int c0 = 0; c0 < 64; c0 += 16) {
+    uint32_t r[16];
+    tmem_ld16(tmem_base + ((uint32_t)(warp * 32) << 16) + (uint32_t)c0, r);
+#pragma unroll
+    for (int i = 0; i < 16; ++i) out[(warp * 32 + lane) * 64 + c0 + i] = __uint_as_float(r[i]);
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 0) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, 64);
+  }
+}
+
+}  // namespace
+
+extern "C" int vcm_umma_probe(int32_t start_row, int32_t sbo_bytes, int32_t use_base_offset, float* out,
+                              void* stream) {
+  VCM_CHECK_ARG(out && start_row >= 0 && sbo_bytes >= 128 && sbo_bytes % 16 == 0, "bad argument");
+  VCM_CHECK_ARG(start_row + 15 * (sbo_bytes / 128) + 8 <= 320, "probe window exceeds the buffer");
+  const int smem_bytes = 320 * 128 + 64 * 128 + 64 + 1024;
+  static bool attr_set = false;
+  if (!attr_set) {
+    cudaFuncSetAttribute(umma_probe_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes);
+    attr_set = true;
+  }
+  umma_probe_kernel<<<1, 128, smem_bytes, (cudaStream_t)stream>>>(start_row, sbo_bytes, use_base_offset, out);
+  VCM_CHECK_LAUNCH();
+  return 0;
+}
