@@ -176,8 +176,8 @@ def conv_roofline(dmc, intra, x, dpb, q):
                 n_tc=sum(1 for r in recs if r[3]), by_shape=by_shape)
 
 
-def oracle_fps(sd_p, sd_i, threads, hh=544, ww=960, frames=1):
-    """CPU oracle port (reference algorithm, PyTorch CPU + C rANS) on a 960x544 crop: seconds per
+def oracle_fps(sd_p, sd_i, threads, hh=576, ww=960, frames=1):
+    """CPU oracle port (reference algorithm, PyTorch CPU + C rANS) on a 960x576 crop: seconds per
     P-frame encode+decode, converted to 1080p-equivalent frames/s by the pixel ratio (the nets are
     fully convolutional, cost is linear in pixels)."""
     from oracle import dcvc_oracle as O

@@ -94,8 +94,9 @@ int vcm_nchw_to_nhwc(const float* src, void* dst, int32_t N, int32_t C, int32_t 
 int vcm_nhwc_to_nchw(const void* src, float* dst, int32_t N, int32_t C, int32_t H, int32_t W,
                      int32_t src_cstride, int32_t dtype, int32_t do_clamp, float lo, float hi,
                      void* stream);
+/* channel-slice copy with optional fp32 <-> bf16 conversion */
 int vcm_copy_channels(const void* src, void* dst, int64_t npix, int32_t C, int32_t src_cstride,
-                      int32_t dst_cstride, int32_t dtype, void* stream);
+                      int32_t dst_cstride, int32_t src_dtype, int32_t dst_dtype, void* stream);
 /* x[n,:,c] (op) vec[n,c]; op 0 = divide, 1 = multiply (video_model.py:280,297,306,326)      */
 int vcm_scale_channels(const void* src, void* dst, const float* vec, int32_t N, int64_t hw,
                        int32_t C, int32_t src_cstride, int32_t dst_cstride, int32_t op,

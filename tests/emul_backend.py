@@ -97,7 +97,7 @@ class EmulBackend:
         return t.clamp(*clamp) if clamp is not None else t
 
     def copy(self, src, dst):
-        dst.dense().copy_(src.dense())
+        dst.dense().copy_(src.dense().to(dst.dtype))
         return dst
 
     def scale(self, src, vec, op, out=None):

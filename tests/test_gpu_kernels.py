@@ -375,3 +375,39 @@ def test_round_and_bits_kernels(B32):
     a, b = torch.rand((2, 3, 40, 50), generator=g), torch.rand((2, 3, 40, 50), generator=g)
     torch.testing.assert_close(B32.sq_err_sum(a.to(dev), b.to(dev)).cpu(), ((a - b) ** 2).reshape(2, -1).sum(1),
                                rtol=1e-5, atol=1e-5)
+
+
+SCALAR_TC_CASES = [
+    # K, Cin(real), Cin_p, Cout, ps, fp32 residual, H, W   -- fp32 outputs / tiny Cout on tcgen05
+    (3, 64, 64, 3, False, False, 40, 56),      # recon_conv
+    (7, 16, 16, 2, False, True, 24, 48),       # SpyNet conv5 + flow residual
+    (1, 64, 64, 8, True, False, 17, 30),       # mv_decoder subpel -> 2-channel flow
+    (7, 8, 16, 32, False, False, 24, 40),      # SpyNet conv1, input padded 8 -> 16 (bf16 out)
+    (3, 3, 16, 64, False, False, 32, 48),      # feature_adaptor_I, frame padded 3 -> 16 (bf16 out)
+]
+
+
+@pytest.mark.parametrize("case", SCALAR_TC_CASES)
+def test_conv_tcgen05_padded_and_fp32_out(B16, case):
+    K, Cin, Cin_p, Cout, ps, use_res, H, W = case
+    g = torch.Generator(device="cpu").manual_seed(200 + SCALAR_TC_CASES.index(case))
+    dev, bf = "cuda:0", torch.bfloat16
+    x = torch.randn((1, Cin, H, W), generator=g).to(dev).to(bf)
+    w = (torch.randn((Cout, Cin, K, K), generator=g) / (Cin * K * K) ** 0.5).to(dev)
+    b = torch.randn((Cout,), generator=g).to(dev)
+    fp32_out = Cout < 16
+    oshape = (1, Cout // 4, 2 * H, 2 * W) if ps else (1, Cout, H, W)
+    res = torch.randn(oshape, generator=g).to(dev) if use_res else None
+    in_map = list(range(Cin)) + [-1] * (Cin_p - Cin) if Cin_p != Cin else None
+    pc = B16.pack_conv(w, b, in_map)
+    assert pc.w_umma is not None
+    from vcm_ts_b200.backend import View
+    xv = View(view_of(x.float(), dtype=bf, cs=Cin_p).t)      # all Cin_p channels; the pad is zero
+    launches = B16.launches
+    out = B16.conv(xv, pc, ps=ps, res=view_of(res) if use_res else None,
+                   out_dtype=torch.float32 if fp32_out else bf)
+    torch.cuda.synchronize()
+    assert B16.launches == launches + 1
+    want = ref_conv(x.float(), w.to(bf).float(), b, 1, None, None, ps, res, None, None)
+    got = nchw(out)
+    assert bool(((got - want).abs() <= 0.01 * want.abs() + 0.02).all()), (got - want).abs().max().item()

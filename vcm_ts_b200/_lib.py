@@ -48,7 +48,7 @@ _PROTOS = {
     "vcm_nchw_to_nhwc": (c_int, [_P, _P, c_int32, c_int32, c_int32, c_int32, c_int32, c_int32, _P]),
     "vcm_nhwc_to_nchw": (c_int, [_P, _P, c_int32, c_int32, c_int32, c_int32, c_int32, c_int32,
                                  c_int32, c_float, c_float, _P]),
-    "vcm_copy_channels": (c_int, [_P, _P, c_int64, c_int32, c_int32, c_int32, c_int32, _P]),
+    "vcm_copy_channels": (c_int, [_P, _P, c_int64, c_int32, c_int32, c_int32, c_int32, c_int32, _P]),
     "vcm_scale_channels": (c_int, [_P, _P, _P, c_int32, c_int64, c_int32, c_int32, c_int32, c_int32,
                                    c_int32, _P]),
     "vcm_maxpool2": (c_int, [_P, _P, c_int32, c_int32, c_int32, c_int32, c_int32, c_int32, c_int32, _P]),

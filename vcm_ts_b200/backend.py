@@ -104,7 +104,7 @@ class CudaBackend:
                                           m.data_ptr() if m is not None else None, self.stream),
               "vcm_pack_conv_weight")
         pc = PackedConv(out, bias.detach().to(self.device, torch.float32).contiguous(), K, cin_p, Cout)
-        if self.precision == "bf16" and cin_p % 16 == 0 and Cout % 16 == 0 and Cout <= 256:
+        if self.precision == "bf16" and cin_p % 16 == 0:
             nbytes = self.L.vcm_conv2d_tc_weight_bytes(Cout, cin_p, K)
             if nbytes > 0:
                 wu = torch.empty((nbytes,), dtype=torch.uint8, device=self.device)
@@ -192,9 +192,9 @@ class CudaBackend:
         return out
 
     def copy(self, src, dst):
-        assert (src.N, src.H, src.W, src.C) == (dst.N, dst.H, dst.W, dst.C) and src.dtype == dst.dtype
+        assert (src.N, src.H, src.W, src.C) == (dst.N, dst.H, dst.W, dst.C)
         check(self.L.vcm_copy_channels(src.ptr, dst.ptr, src.N * src.H * src.W, src.C, src.cs, dst.cs,
-                                       _code(src.dtype), self.stream), "vcm_copy_channels")
+                                       _code(src.dtype), _code(dst.dtype), self.stream), "vcm_copy_channels")
         self.launches += 1
         return dst
 

@@ -330,8 +330,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       const bool valid = oy < P.Ho && ox < P.Wo;
       const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(g * G.bn);
       const int cbase = nt * G.bn;
-      if (G.bn % 64 == 0) epilogue_tile<64>(P, G, n, oy, ox, valid, cbase, taddr, &tfull[g], acc_phase);
-      else if (G.bn % 32 == 0) epilogue_tile<32>(P, G, n, oy, ox, valid, cbase, taddr, &tfull[g], acc_phase);
+      if (G.bn % 32 == 0) epilogue_tile<32>(P, G, n, oy, ox, valid, cbase, taddr, &tfull[g], acc_phase);
       else epilogue_tile<16>(P, G, n, oy, ox, valid, cbase, taddr, &tfull[g], acc_phase);
       tc_fence_before();
       mbar_arrive(&tempty[g]);

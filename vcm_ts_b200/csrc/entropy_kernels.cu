@@ -26,7 +26,8 @@ inline int ew_grid(int64_t total) {
 
 __device__ __forceinline__ uint8_t scale_index(float sc, float lmin, float lstep) {
   const float s = fmaxf(sc, 1e-5f);
-  float v = __fdiv_rn(__fsub_rn(logf(s), lmin), lstep);
+  // log through double: the correctly rounded fp32 log, the best match for the reference's CPU logf
+  float v = __fdiv_rn(__fsub_rn((float)log((double)s), lmin), lstep);
   v = fminf(fmaxf(v, 0.f), 255.f);
   return (uint8_t)(int)v;
 }

@@ -54,15 +54,15 @@ __global__ void nhwc_to_nchw_kernel(const T* __restrict__ src, float* __restrict
   }
 }
 
-template <typename T>
-__global__ void copy_channels_kernel(const T* __restrict__ src, T* __restrict__ dst, int64_t npix,
+template <typename T, typename TO>
+__global__ void copy_channels_kernel(const T* __restrict__ src, TO* __restrict__ dst, int64_t npix,
                                      int C, int src_cs, int dst_cs) {
   const int64_t total = npix * C;
   for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total;
        i += (int64_t)gridDim.x * blockDim.x) {
     const int64_t p = i / C;
     const int c = (int)(i - p * C);
-    dst[p * dst_cs + c] = src[p * src_cs + c];
+    st_from_float(dst + p * dst_cs + c, ld_as_float(src + p * src_cs + c));
   }
 }
 
@@ -185,11 +185,24 @@ extern "C" int vcm_nhwc_to_nchw(const void* src, float* dst, int32_t N, int32_t 
 }
 
 extern "C" int vcm_copy_channels(const void* src, void* dst, int64_t npix, int32_t C,
-                                 int32_t src_cstride, int32_t dst_cstride, int32_t dtype,
-                                 void* stream) {
+                                 int32_t src_cstride, int32_t dst_cstride, int32_t src_dtype,
+                                 int32_t dst_dtype, void* stream) {
   VCM_CHECK_ARG(src && dst && npix > 0 && C > 0, "bad argument");
-  VCM_DISPATCH_DTYPE(dtype, (copy_channels_kernel<T><<<ew_grid(npix * C), 256, 0, (cudaStream_t)stream>>>(
-                                (const T*)src, (T*)dst, npix, C, src_cstride, dst_cstride)));
+  const int g = ew_grid(npix * C);
+  cudaStream_t s = (cudaStream_t)stream;
+  using bf = __nv_bfloat16;
+  if (src_dtype == VCM_F32 && dst_dtype == VCM_F32)
+    copy_channels_kernel<float, float><<<g, 256, 0, s>>>((const float*)src, (float*)dst, npix, C, src_cstride, dst_cstride);
+  else if (src_dtype == VCM_F32 && dst_dtype == VCM_BF16)
+    copy_channels_kernel<float, bf><<<g, 256, 0, s>>>((const float*)src, (bf*)dst, npix, C, src_cstride, dst_cstride);
+  else if (src_dtype == VCM_BF16 && dst_dtype == VCM_F32)
+    copy_channels_kernel<bf, float><<<g, 256, 0, s>>>((const bf*)src, (float*)dst, npix, C, src_cstride, dst_cstride);
+  else if (src_dtype == VCM_BF16 && dst_dtype == VCM_BF16)
+    copy_channels_kernel<bf, bf><<<g, 256, 0, s>>>((const bf*)src, (bf*)dst, npix, C, src_cstride, dst_cstride);
+  else {
+    vcm_set_error("vcm_copy_channels: bad dtype");
+    return 1;
+  }
   VCM_CHECK_LAUNCH();
   return 0;
 }

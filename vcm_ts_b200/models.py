@@ -260,7 +260,8 @@ class DMC(CompressionModel):
         rt = self._runtime()
         g, B = rt.graph, rt.B
         if dpb["ref_feature"] is None:
-            f = g.conv("feature_adaptor_I", B.from_nchw(dpb["ref_frame"]))
+            xin, m = g.frame_input(dpb["ref_frame"])
+            f = g.conv("feature_adaptor_I", xin, in_map=m)
         else:
             f = g.conv("feature_adaptor_P", B.from_nchw(dpb["ref_feature"]))
         t, ta = g.conv_t("feature_extractor.conv1", f, 0.01)
@@ -562,7 +563,8 @@ class IntraNoAR(CompressionModel):
 
     def _trunk(self, rt, x, q, want_full):
         g, B = rt.graph, rt.B
-        y = B.scale(g.analysis("enc", B.from_nchw(x)), q, "div")
+        xin, m = g.frame_input(x)
+        y = B.scale(g.analysis("enc", xin, m), q, "div")
         z = g.hyper_analysis("hyper_enc", y)
         z_sym = B.empty((x.shape[0], self.N, z.H, z.W), torch.int16)
         z_hat = B.round_latent(z, sym=z_sym)

@@ -49,10 +49,21 @@ class Graph:
         return self.conv(pre + ".conv2", t, **kw)
 
     # ---- layers.py:42-73
-    def residual_block_with_stride(self, pre, x):
-        idn = self.conv(pre + ".downsample", x, stride=2)
-        t = self.conv(pre + ".conv1", x, stride=2, post=0.01)
+    def residual_block_with_stride(self, pre, x, in_map=None):
+        idn = self.conv(pre + ".downsample", x, in_map=in_map, stride=2)
+        t = self.conv(pre + ".conv1", x, in_map=in_map, stride=2, post=0.01)
         return self.conv(pre + ".conv2", t, post=0.1, res=idn)
+
+    def frame_input(self, x_nchw):
+        """NCHW fp32 frame -> (NHWC view, in_map).  Tensor-core mode pads the 3 channels to 16 (zero
+        weights on the pad) so first-layer convs run on tcgen05; exact mode keeps 3 channels."""
+        B = self.B
+        if not B.use_twin:
+            return B.from_nchw(x_nchw), None
+        N, C, H, W = x_nchw.shape
+        buf = B.new(N, H, W, 16, zero=True)
+        B.from_nchw(x_nchw, out=buf.sl(0, C))
+        return buf, list(range(C)) + [-1] * (16 - C)
 
     # ---- layers.py:76-101
     def residual_block_upsample(self, pre, x):
@@ -66,8 +77,8 @@ class Graph:
         return self.conv(pre + ".conv2", t, post=slope, res=x)
 
     # ---- video_net.py:226-235
-    def analysis(self, pre, x):
-        x = self.residual_block_with_stride(pre + ".0", x)
+    def analysis(self, pre, x, in_map=None):
+        x = self.residual_block_with_stride(pre + ".0", x, in_map)
         x = self.residual_block(pre + ".1", x)
         x = self.residual_block_with_stride(pre + ".2", x)
         x = self.residual_block(pre + ".3", x)
@@ -156,7 +167,14 @@ class Graph:
             flow_up = B.flow_up2(flow, out=buf.sl(6, 8), gain=2.0)
             B.warp(im2[k], flow_up, out=buf.sl(3, 6))
             b = f"{pre}.moduleBasic.{lv}"
-            t = self.conv(b + ".conv1", buf, post=0.0, out_dtype=B.act_dtype)
+            if B.use_twin:
+                # tensor-core mode: bf16 copy of the level input padded to 16 channels (zero weights
+                # on the pad) so the 7x7 8->32 conv runs on tcgen05 as well
+                buf16 = B.new(N, buf.H, buf.W, 16, dtype=B.act_dtype, zero=True)
+                B.copy(buf, buf16.sl(0, 8))
+                t = self.conv(b + ".conv1", buf16, in_map=list(range(8)) + [-1] * 8, post=0.0)
+            else:
+                t = self.conv(b + ".conv1", buf, post=0.0, out_dtype=B.act_dtype)
             t = self.conv(b + ".conv2", t, post=0.0)
             t = self.conv(b + ".conv3", t, post=0.0)
             t = self.conv(b + ".conv4", t, post=0.0)
