@@ -85,6 +85,8 @@ int vcm_conv2d_tc_fwd(const vcm_conv_desc* d, const void* x, const void* w_umma,
  * given stride between 8-row groups; out[128*64] fp32 = the A rows the tensor core read.     */
 int vcm_umma_probe(int32_t start_row, int32_t sbo_bytes, int32_t use_base_offset, float* out,
                    void* stream);
+/* issue-rate probe: `iters` back-to-back 128xNx16 bf16 MMAs; out[0] = SM cycles, out[1] = iters */
+int vcm_umma_rate(int32_t N, int32_t iters, long long* out, void* stream);
 
 /* ---- layout / elementwise glue ------------------------------------------------------- */
 /* NCHW fp32 -> NHWC view (dtype) ; callers' tensors are NCHW fp32 (video_coder.py:99-117)  */

@@ -82,3 +82,59 @@ extern "C" int vcm_umma_probe(int32_t start_row, int32_t sbo_bytes, int32_t use_
   VCM_CHECK_LAUNCH();
   return 0;
 }
+
+// ---- MMA issue-rate probe: `iters` back-to-back 128 x N x 16 bf16 MMAs on fixed smem operands, one
+// commit at the end; out[0] = SM cycles from first issue to completion, out[1] = iters.
+namespace {
+__global__ void __launch_bounds__(128, 1) umma_rate_kernel(int N, int iters, long long* __restrict__ out) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  uint8_t* sA = smem;                 // 128 x 128 B
+  uint8_t* sB = smem + 128 * 128;     // 256 x 128 B
+  uint64_t* bar = reinterpret_cast<uint64_t*>(sB + 256 * 128);
+  uint32_t* slot = reinterpret_cast<uint32_t*>(bar + 1);
+  for (int i = threadIdx.x; i < (128 + 256) * 128 / 4; i += blockDim.x) reinterpret_cast<uint32_t*>(smem)[i] = 0;
+  if (threadIdx.x == 0) {
+    mbar_init(bar, 1);
+    fence_barrier_init();
+  }
+  fence_proxy_async();
+  if ((threadIdx.x >> 5) == 0) tmem_alloc(slot, 512);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *slot;
+  if (threadIdx.x == 0) {
+    const uint64_t adesc = make_smem_desc(smem_u32(sA), 1024u, 2u);
+    const uint64_t bdesc = make_smem_desc(smem_u32(sB), 1024u, 2u);
+    const uint32_t idesc = make_idesc_bf16(128, N);
+    const long long t0 = clock64();
+    for (int i = 0; i < iters; ++i) umma_bf16(tmem_base + (uint32_t)((i & 1) * 256), adesc + (uint64_t)(2 * (i & 3)),
+                                              bdesc + (uint64_t)(2 * (i & 3)), idesc, 1u);
+    umma_commit(bar);
+    mbar_wait(bar, 0);
+    const long long t1 = clock64();
+    out[0] = t1 - t0;
+    out[1] = iters;
+  }
+  tc_fence_before();
+  __syncthreads();
+  if ((threadIdx.x >> 5) == 0) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, 512);
+  }
+}
+}  // namespace
+
+extern "C" int vcm_umma_rate(int32_t N, int32_t iters, long long* out, void* stream) {
+  VCM_CHECK_ARG(out && N >= 16 && N <= 256 && N % 16 == 0 && iters > 0, "bad argument");
+  const int smem_bytes = (128 + 256) * 128 + 64 + 1024;
+  static bool attr_set = false;
+  if (!attr_set) {
+    cudaFuncSetAttribute(umma_rate_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes);
+    attr_set = true;
+  }
+  umma_rate_kernel<<<1, 128, smem_bytes, (cudaStream_t)stream>>>(N, iters, out);
+  VCM_CHECK_LAUNCH();
+  return 0;
+}
