@@ -1,0 +1,325 @@
+// vcm_ts_b200/csrc/conv_halo.cu -- stride-1 tensor-core convolution for sm_100a: implicit GEMM on
+// tcgen05.mma with a HALO activation tile and (where they fit) shared-memory-RESIDENT weights.
+//
+// Why.  The per-tap engine (conv_tc.cu) re-fetches the 128-pixel activation tile and the weight slab
+// for each of the K*K taps: 216 KB of L2->SM traffic per 128x64 output tile of a 3x3 64->64 conv,
+// which ncu shows is what bounds it (profiles/ncu_conv64_pertap_r01.json: 4.1 GB through the
+// crossbar per launch, tensor pipe 12 %).  Here
+//   * ONE 4-D TMA box {CHUNK, 8+K-1, 16*MH+K-1, 1} brings the tile plus its halo (zero-filled outside
+//     the image = the conv padding); every tap is then just a different START ADDRESS of the same
+//     shared-memory tile: the UMMA descriptor addresses row m = 8*y + x of the A operand at
+//     start + y*SBO + x*rowbytes with SBO = (8+K-1)*rowbytes, start = ((ky*(8+K-1) + kx)*rowbytes.
+//     This relies on the 128/64/32-byte swizzle being a function of the absolute shared-memory
+//     address (measured: vcm_umma_probe, profiles/umma_probe_r01.json), so TMA-written tiles can be
+//     read at any row offset / row-group stride;
+//   * weights whose taps*Cin*Cout bf16 fit beside the A ring (3x3 64->64: 72 KB) are loaded ONCE per
+//     persistent CTA; otherwise weight slabs stream through their own ring, and the item grows to
+//     M = 256 (two 8x16 halves, MH = 2) so each slab is used for twice the pixels.
+// Traffic per 3x3 64->64 tile drops from 216 KB to 23 KB.
+//
+// Roles (352 threads): warp 0 = activation TMA, warp 10 = weight TMA, warp 1 = MMA issue + TMEM,
+// warps 2-5 / 6-9 = two epilogue warpgroups (one per TMEM accumulator buffer), see tc_epilogue.cuh.
+#include <mutex>
+
+#include "conv_common.cuh"
+#include "tc_epilogue.cuh"
+#include "tc_host.cuh"
+using namespace tc;
+
+namespace {
+
+constexpr int HTW = 8, HTH = 16;
+constexpr int H_THREADS = 352;
+constexpr int H_MAX_A = 6, H_MAX_B = 12;
+
+struct HaloGeom {
+  int nchunks, ntaps, a_stages, b_stages, resident;
+  int a_bytes, a_stage_bytes;
+  int b_bytes, b_slot_bytes, b_base;
+  int hw, hh, mh;
+  int tiles_x, tiles_y, n_tiles, num_items;
+  int bn, cout_p, tmem_cols, scalar_epi;
+  uint32_t idesc;
+};
+
+template <int CHUNK>
+__global__ void __launch_bounds__(H_THREADS, 1)
+conv_halo_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                 const ConvParams P, const HaloGeom G) {
+  constexpr uint32_t LAYOUT = CHUNK == 64 ? 2u : (CHUNK == 32 ? 4u : 6u);
+  constexpr uint32_t ROWB = CHUNK * 2u;      // bytes per pixel row of the A tile / per weight row
+  constexpr int KSTEPS = CHUNK / 16;
+
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  const int b_slots = G.resident ? G.ntaps * G.nchunks : G.b_stages;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + G.b_base + (size_t)b_slots * G.b_slot_bytes);
+  uint64_t* afull = bars;
+  uint64_t* aempty = afull + H_MAX_A;
+  uint64_t* bfull = aempty + H_MAX_A;
+  uint64_t* bempty = bfull + H_MAX_B;
+  uint64_t* tfull = bempty + H_MAX_B;
+  uint64_t* tempty = tfull + 2;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + 2);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int sp_tiles = G.tiles_x * G.tiles_y;
+  const uint32_t sbo = (uint32_t)G.hw * ROWB;
+
+  if (threadIdx.x == 0) {
+    prefetch_tmap(&tmA);
+    prefetch_tmap(&tmB);
+    for (int s = 0; s < H_MAX_A; ++s) { mbar_init(&afull[s], 1); mbar_init(&aempty[s], 1); }
+    for (int s = 0; s < H_MAX_B; ++s) { mbar_init(&bfull[s], 1); mbar_init(&bempty[s], 1); }
+    for (int a = 0; a < 2; ++a) { mbar_init(&tfull[a], 1); mbar_init(&tempty[a], 128); }
+    fence_barrier_init();
+  }
+  if (warp == 1) tmem_alloc(tmem_slot, (uint32_t)G.tmem_cols);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // ============================ activation producer: one halo box per (item, chunk) ==========
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int item = blockIdx.x; item < G.num_items; item += gridDim.x) {
+        const int sp = item / G.n_tiles;
+        const int n = sp / sp_tiles, rem = sp - n * sp_tiles;
+        const int y0 = (rem / G.tiles_x) * (HTH * G.mh), x0 = (rem % G.tiles_x) * HTW;
+        for (int ch = 0; ch < G.nchunks; ++ch) {
+          mbar_wait(&aempty[stage], phase ^ 1u);
+          mbar_expect_tx(&afull[stage], (uint32_t)G.a_bytes);
+          tma_load_4d(smem_u32(smem + (size_t)stage * G.a_stage_bytes), &tmA, &afull[stage], ch * CHUNK,
+                      x0 - P.pad, y0 - P.pad, n);
+          if (++stage == G.a_stages) { stage = 0; phase ^= 1u; }
+        }
+      }
+    }
+  } else if (warp == 10) {
+    // ============================ weight producer ==============================================
+    if (lane == 0) {
+      if (G.resident) {
+        const int slabs = G.ntaps * G.nchunks;
+        mbar_expect_tx(&bfull[0], (uint32_t)(slabs * G.b_bytes));
+        for (int s = 0; s < slabs; ++s)
+          tma_load_2d(smem_u32(smem + G.b_base + (size_t)s * G.b_slot_bytes), &tmB, &bfull[0], 0, s * G.cout_p);
+      } else {
+        int stage = 0;
+        uint32_t phase = 0;
+        for (int item = blockIdx.x; item < G.num_items; item += gridDim.x) {
+          const int nt = item % G.n_tiles;
+          for (int ch = 0; ch < G.nchunks; ++ch)
+            for (int tap = 0; tap < G.ntaps; ++tap) {
+              mbar_wait(&bempty[stage], phase ^ 1u);
+              mbar_expect_tx(&bfull[stage], (uint32_t)G.b_bytes);
+              tma_load_2d(smem_u32(smem + G.b_base + (size_t)stage * G.b_slot_bytes), &tmB, &bfull[stage], 0,
+                          (tap * G.nchunks + ch) * G.cout_p + nt * G.bn);
+              if (++stage == G.b_stages) { stage = 0; phase ^= 1u; }
+            }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ============================ MMA issuer (one thread) ======================================
+    if (lane == 0) {
+      int as = 0, bs = 0, acc = 0;
+      uint32_t aphase = 0, bphase = 0, acc_phase = 0;
+      if (G.resident) {
+        mbar_wait(&bfull[0], 0);
+        tc_fence_after();
+      }
+      const uint32_t b_region = smem_u32(smem + G.b_base);
+      for (int item = blockIdx.x; item < G.num_items; item += gridDim.x) {
+        mbar_wait(&tempty[acc], acc_phase ^ 1u);
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + (uint32_t)(acc * G.mh * G.bn);
+        for (int ch = 0; ch < G.nchunks; ++ch) {
+          mbar_wait(&afull[as], aphase);
+          tc_fence_after();
+          const uint32_t a_base = smem_u32(smem + (size_t)as * G.a_stage_bytes);
+          for (int tap = 0; tap < G.ntaps; ++tap) {
+            const int ky = tap / P.K, kx = tap - ky * P.K;
+            uint32_t b_addr;
+            if (G.resident) {
+              b_addr = b_region + (uint32_t)((tap * G.nchunks + ch) * G.b_slot_bytes);
+            } else {
+              mbar_wait(&bfull[bs], bphase);
+              tc_fence_after();
+              b_addr = b_region + (uint32_t)(bs * G.b_slot_bytes);
+            }
+            const uint64_t bdesc = make_smem_desc(b_addr, 8u * ROWB, LAYOUT);
+            for (int h = 0; h < G.mh; ++h) {
+              const uint32_t a_addr = a_base + (uint32_t)(((ky + h * HTH) * G.hw + kx)) * ROWB;
+              const uint64_t adesc = make_smem_desc(a_addr, sbo, LAYOUT);
+#pragma unroll
+              for (int k = 0; k < KSTEPS; ++k)
+                umma_bf16(d_tmem + (uint32_t)(h * G.bn), adesc + (uint64_t)(2 * k), bdesc + (uint64_t)(2 * k),
+                          G.idesc, (ch > 0 || tap > 0 || k > 0) ? 1u : 0u);
+            }
+            if (!G.resident) {
+              umma_commit(&bempty[bs]);
+              if (++bs == G.b_stages) { bs = 0; bphase ^= 1u; }
+            }
+          }
+          umma_commit(&aempty[as]);
+          if (++as == G.a_stages) { as = 0; aphase ^= 1u; }
+        }
+        umma_commit(&tfull[acc]);
+        acc ^= 1;
+        if (acc == 0) acc_phase ^= 1u;
+      }
+    }
+  } else {
+    // ============ epilogue: warpgroup g (warps 2-5 / 6-9) owns accumulator buffer g ============
+    const int g = (warp - 2) >> 2;
+    const int q = warp & 3;
+    const int m = q * 32 + lane;
+    const int py = m / HTW, px = m % HTW;
+    uint32_t acc_phase = 0;
+    int local = 0;
+    for (int item = blockIdx.x; item < G.num_items; item += gridDim.x, ++local) {
+      if ((local & 1) != g) continue;
+      const int nt = item % G.n_tiles, sp = item / G.n_tiles;
+      const int n = sp / sp_tiles, rem = sp - n * sp_tiles;
+      const int ox = (rem % G.tiles_x) * HTW + px;
+      const int cbase = nt * G.bn;
+      for (int h = 0; h < G.mh; ++h) {
+        const int oy = (rem / G.tiles_x) * (HTH * G.mh) + h * HTH + py;
+        const bool valid = oy < P.Ho && ox < P.Wo;
+        const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)((g * G.mh + h) * G.bn);
+        if (G.bn % 32 == 0) epilogue_tile<32, HaloGeom>(P, G, n, oy, ox, valid, cbase, taddr, &tfull[g], acc_phase);
+        else epilogue_tile<16, HaloGeom>(P, G, n, oy, ox, valid, cbase, taddr, &tfull[g], acc_phase);
+      }
+      tc_fence_before();
+      mbar_arrive(&tempty[g]);
+      acc_phase ^= 1u;
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, (uint32_t)G.tmem_cols);
+  }
+}
+
+}  // namespace
+
+// ---------------------------------------------------------------------------------- host
+int vcm_conv_halo_launch(const vcm_conv_desc* d, const ConvParams& P, const void* x, const void* w_umma,
+                         cudaStream_t stream) {
+  if (P.stride != 1) return 3;
+  EncodeTiledFn enc = get_encode_fn();
+  if (!enc) {
+    vcm_set_error("vcm_conv_halo_launch: cuTensorMapEncodeTiled unavailable");
+    return 1;
+  }
+  HaloGeom G;
+  memset(&G, 0, sizeof(G));
+  const int chunk = pick_chunk(P.Cin);
+  pick_n_tiling(P.Cout, G.cout_p, G.bn, G.n_tiles);
+  G.nchunks = P.Cin / chunk;
+  G.ntaps = P.K * P.K;
+  G.hw = HTW + P.K - 1;
+  G.b_bytes = G.bn * chunk * 2;
+  G.b_slot_bytes = round_up(G.b_bytes, 1024);
+  const int slabs = G.ntaps * G.nchunks;
+  const int budget = SMEM_LIMIT - 1024 - 1024;   // alignment slack + barriers
+  const bool vec = d->out_dtype == VCM_BF16 && d->Cout % 16 == 0;
+  G.scalar_epi = vec ? 0 : (d->out_dtype == VCM_F32 ? 2 : 1);
+
+  auto a_stage = [&](int mh) { return round_up(G.hw * (HTH * mh + P.K - 1) * chunk * 2, 1024); };
+  // resident weights if they leave room for >= 3 activation stages
+  G.resident = (G.n_tiles == 1) && (slabs * G.b_slot_bytes + 3 * a_stage(1) <= budget);
+  if (G.resident) {
+    G.mh = 1;
+    G.b_stages = 0;
+    G.a_stage_bytes = a_stage(1);
+    G.a_stages = (budget - slabs * G.b_slot_bytes) / G.a_stage_bytes;
+  } else {
+    G.mh = (G.bn <= 128 && P.Ho > HTH) ? 2 : 1;
+    G.a_stage_bytes = a_stage(G.mh);
+    G.a_stages = 3;
+    if (G.a_stages * G.a_stage_bytes > budget / 2) G.a_stages = 2;
+    if (G.a_stages * G.a_stage_bytes + 2 * G.b_slot_bytes > budget) return 3;
+    G.b_stages = (budget - G.a_stages * G.a_stage_bytes) / G.b_slot_bytes;
+    if (G.b_stages > H_MAX_B) G.b_stages = H_MAX_B;
+    // spend what is left on more activation stages
+    const int left = budget - G.b_stages * G.b_slot_bytes - G.a_stages * G.a_stage_bytes;
+    G.a_stages += left / G.a_stage_bytes;
+  }
+  if (G.a_stages > H_MAX_A) G.a_stages = H_MAX_A;
+  if (G.a_stages < 2) return 3;
+  G.hh = HTH * G.mh + P.K - 1;
+  G.a_bytes = G.hw * G.hh * chunk * 2;
+  G.b_base = G.a_stages * G.a_stage_bytes;
+  G.tiles_x = cdiv(P.Wo, HTW);
+  G.tiles_y = cdiv(P.Ho, HTH * G.mh);
+  G.num_items = G.tiles_x * G.tiles_y * P.N * G.n_tiles;
+  int cols = 32;
+  while (cols < 2 * G.mh * G.bn) cols <<= 1;
+  if (cols > 512) return 3;
+  G.tmem_cols = cols;
+  G.idesc = make_idesc_bf16(128, G.bn);
+
+  CUtensorMap tmA, tmB;
+  {
+    cuuint64_t dims[4] = {(cuuint64_t)P.Cin, (cuuint64_t)P.W, (cuuint64_t)P.H, (cuuint64_t)P.N};
+    cuuint64_t strides[3] = {(cuuint64_t)P.in_cs * 2, (cuuint64_t)P.W * P.in_cs * 2,
+                             (cuuint64_t)P.H * P.W * P.in_cs * 2};
+    cuuint32_t box[4] = {(cuuint32_t)chunk, (cuuint32_t)G.hw, (cuuint32_t)G.hh, 1};
+    cuuint32_t estr[4] = {1, 1, 1, 1};
+    CUresult r = enc(&tmA, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(x), dims, strides, box, estr,
+                     CU_TENSOR_MAP_INTERLEAVE_NONE, swizzle_of(chunk), CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) {
+      vcm_set_error("vcm_conv_halo_launch: cuTensorMapEncodeTiled(A) failed (%d)", (int)r);
+      return 1;
+    }
+  }
+  {
+    cuuint64_t dims[2] = {(cuuint64_t)chunk, (cuuint64_t)slabs * G.cout_p};
+    cuuint64_t strides[1] = {(cuuint64_t)chunk * 2};
+    cuuint32_t box[2] = {(cuuint32_t)chunk, (cuuint32_t)G.bn};
+    cuuint32_t estr[2] = {1, 1};
+    CUresult r = enc(&tmB, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(w_umma), dims, strides, box,
+                     estr, CU_TENSOR_MAP_INTERLEAVE_NONE, swizzle_of(chunk), CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) {
+      vcm_set_error("vcm_conv_halo_launch: cuTensorMapEncodeTiled(B) failed (%d)", (int)r);
+      return 1;
+    }
+  }
+  const int b_slots = G.resident ? slabs : G.b_stages;
+  int smem_bytes = G.b_base + b_slots * G.b_slot_bytes + 1024 + 1024;
+  if (smem_bytes < 120 * 1024) smem_bytes = 120 * 1024;   // one CTA per SM (TMEM is per CTA)
+  const int grid = G.num_items < num_sms() ? G.num_items : num_sms();
+#define LAUNCH_HALO(CH)                                                                                  \
+  do {                                                                                                   \
+    static bool attr_set = false;                                                                        \
+    if (!attr_set) {                                                                                     \
+      cudaError_t e = cudaFuncSetAttribute(conv_halo_kernel<CH>, cudaFuncAttributeMaxDynamicSharedMemorySize, \
+                                           SMEM_LIMIT);                                                  \
+      if (e != cudaSuccess) {                                                                            \
+        vcm_set_error("vcm_conv_halo_launch: cudaFuncSetAttribute: %s", cudaGetErrorString(e));          \
+        return 1;                                                                                        \
+      }                                                                                                  \
+      attr_set = true;                                                                                   \
+    }                                                                                                    \
+    conv_halo_kernel<CH><<<grid, H_THREADS, smem_bytes, stream>>>(tmA, tmB, P, G);                       \
+  } while (0)
+  if (chunk == 64) LAUNCH_HALO(64);
+  else if (chunk == 32) LAUNCH_HALO(32);
+  else LAUNCH_HALO(16);
+#undef LAUNCH_HALO
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) {
+    vcm_set_error("vcm_conv_halo_launch: launch failed: %s", cudaGetErrorString(e));
+    return 1;
+  }
+  return 0;
+}

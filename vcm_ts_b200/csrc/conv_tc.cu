@@ -20,9 +20,11 @@
 // CTAs are persistent: grid = min(work items, #SM), work items round-robin, N tiles of one spatial
 // tile adjacent so the activation boxes are re-read from L2.
 #include <mutex>
+#include <stdlib.h>
 
 #include "conv_common.cuh"
 #include "tc_epilogue.cuh"
+#include "tc_host.cuh"
 using namespace tc;
 
 namespace {
@@ -192,51 +194,7 @@ __global__ void pack_umma_kernel(const float* __restrict__ w, __nv_bfloat16* __r
 }
 
 // ---------------------------------------------------------------------------------- host
-typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
-                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*,
-                                  CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion,
-                                  CUtensorMapFloatOOBfill);
-
-EncodeTiledFn get_encode_fn() {
-  static EncodeTiledFn fn = nullptr;
-  static std::once_flag once;
-  std::call_once(once, [] {
-    void* p = nullptr;
-    cudaDriverEntryPointQueryResult q;
-    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
-        q == cudaDriverEntryPointSuccess)
-      fn = reinterpret_cast<EncodeTiledFn>(p);
-  });
-  return fn;
-}
-
-int pick_chunk(int cin) { return cin % 64 == 0 ? 64 : (cin % 32 == 0 ? 32 : 16); }
-CUtensorMapSwizzle swizzle_of(int chunk) {
-  return chunk == 64 ? CU_TENSOR_MAP_SWIZZLE_128B : (chunk == 32 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_32B);
-}
-int round_up(int v, int m) { return (v + m - 1) / m * m; }
-
-// N tiling: Cout padded to 16; above 256 split into the fewest equal tiles that are multiples of 16
-void pick_n_tiling(int cout, int& cout_p, int& bn, int& n_tiles) {
-  cout_p = round_up(cout, 16);
-  n_tiles = 1;
-  while (cout_p / n_tiles > 256 || cout_p % n_tiles || (cout_p / n_tiles) % 16) ++n_tiles;
-  bn = cout_p / n_tiles;
-}
-
-int num_sms() {
-  static int n = 0;
-  if (!n) {
-    int dev = 0;
-    cudaGetDevice(&dev);
-    cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
-    if (n <= 0) n = 148;
-  }
-  return n;
-}
-
 constexpr int SMEM_BAR_BYTES = 512;
-constexpr int SMEM_LIMIT = 227 * 1024;
 
 }  // namespace
 
@@ -302,6 +260,13 @@ extern "C" int vcm_conv2d_tc_fwd(const vcm_conv_desc* d, const void* x, const vo
                       ((uintptr_t)y2 & 7) == 0 && ((uintptr_t)bias & 15) == 0 && ((uintptr_t)res_scale & 15) == 0,
                   "output / residual views must be 8-byte aligned");
   P.x = x; P.bias = bias; P.res = res; P.res_scale = res_scale; P.res2 = res2; P.y = y; P.y2 = y2;
+
+  // stride-1 shapes go to the halo-tile engine (conv_halo.cu) unless VCM_TC_PERTAP=1 forces this one
+  static const bool force_pertap = getenv("VCM_TC_PERTAP") && getenv("VCM_TC_PERTAP")[0] == '1';
+  if (P.stride == 1 && !force_pertap) {
+    const int rc = vcm_conv_halo_launch(d, P, x, w_umma, (cudaStream_t)stream);
+    if (rc != 3) return rc;
+  }
 
   EncodeTiledFn enc = get_encode_fn();
   VCM_CHECK_ARG(enc != nullptr, "cuTensorMapEncodeTiled unavailable");

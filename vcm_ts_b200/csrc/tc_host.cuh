@@ -1,0 +1,62 @@
+// vcm_ts_b200/csrc/tc_host.cuh -- host-side helpers shared by the tcgen05 conv engines:
+// driver entry point for cuTensorMapEncodeTiled, K-chunk / swizzle / N-tiling choices.
+#pragma once
+#include <cuda.h>
+#include <mutex>
+
+#include "common.cuh"
+
+namespace tc {
+
+// ---------------------------------------------------------------------------------- host
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*,
+                                  CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion,
+                                  CUtensorMapFloatOOBfill);
+
+inline EncodeTiledFn get_encode_fn() {
+  static EncodeTiledFn fn = nullptr;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeTiledFn>(p);
+  });
+  return fn;
+}
+
+inline int pick_chunk(int cin) { return cin % 64 == 0 ? 64 : (cin % 32 == 0 ? 32 : 16); }
+inline CUtensorMapSwizzle swizzle_of(int chunk) {
+  return chunk == 64 ? CU_TENSOR_MAP_SWIZZLE_128B : (chunk == 32 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_32B);
+}
+inline int round_up(int v, int m) { return (v + m - 1) / m * m; }
+
+// N tiling: Cout padded to 16; above 256 split into the fewest equal tiles that are multiples of 16
+inline void pick_n_tiling(int cout, int& cout_p, int& bn, int& n_tiles) {
+  cout_p = round_up(cout, 16);
+  n_tiles = 1;
+  while (cout_p / n_tiles > 256 || cout_p % n_tiles || (cout_p / n_tiles) % 16) ++n_tiles;
+  bn = cout_p / n_tiles;
+}
+
+inline int num_sms() {
+  static int n = 0;
+  if (!n) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
+    if (n <= 0) n = 148;
+  }
+  return n;
+}
+
+constexpr int SMEM_LIMIT = 227 * 1024;
+
+}  // namespace tc
+
+// stride-1 halo engine (conv_halo.cu); returns 0 ok, 1 error, 3 = shape not taken (use per-tap)
+struct ConvParams;
+int vcm_conv_halo_launch(const vcm_conv_desc* d, const ConvParams& P, const void* x, const void* w_umma,
+                         cudaStream_t stream);
