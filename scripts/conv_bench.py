@@ -19,6 +19,8 @@ from vcm_ts_b200.backend import CudaBackend, View  # noqa: E402
 SHAPES = {
     # name: (K, stride, Cin, Cout, H, W, res, ps)
     "c64_64_full": (3, 1, 64, 64, 1088, 1920, True, False),
+    "c64_64_full_nores": (3, 1, 64, 64, 1088, 1920, False, False),
+    "k1_64_64_full_nores": (1, 1, 64, 64, 1088, 1920, False, False),
     "c64_64_half": (3, 1, 64, 64, 544, 960, True, False),
     "c128_128_q": (3, 1, 128, 128, 272, 480, True, False),
     "c128_64_full": (3, 1, 128, 64, 1088, 1920, False, False),
@@ -44,7 +46,7 @@ def main():
         K, stride, Cin, Cout, H, W, use_res, ps = SHAPES[name]
         g = torch.Generator().manual_seed(0)
         w = torch.randn((Cout, Cin, K, K), generator=g) / (Cin * K * K) ** 0.5
-        pc = B.pack_conv(w.cuda(), torch.zeros(Cout).cuda())
+        pc = B.pack_conv(w.cuda(), torch.zeros(Cout).cuda(), ps=ps)
         nbuf = max(2, int(300e6 // (H * W * Cin * 2)) + 1)
         nbuf = min(nbuf, 8)
         xs = [View(torch.randn((1, H, W, Cin), device="cuda").to(bf)) for _ in range(nbuf)]

@@ -32,7 +32,7 @@ class EmulBackend:
     def empty(self, shape, dtype):
         return torch.zeros(shape, dtype=dtype)
 
-    def pack_conv(self, weight, bias, in_map=None, cin_p=None):
+    def pack_conv(self, weight, bias, in_map=None, cin_p=None, ps=False):
         w = weight.detach().float()
         Cout, Cin, K, _ = w.shape
         if in_map is not None:

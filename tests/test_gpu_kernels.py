@@ -168,6 +168,12 @@ TC_CASES = [
     (3, 2, 64, 64, 32, 64, 1, 0.01, False, False, False, False, 0.01),
     (3, 2, 128, 64, 48, 32, 2, None, False, False, False, False, None),
     (1, 2, 64, 64, 32, 32, 1, None, False, False, False, False, None),
+    (3, 1, 64, 128, 19, 37, 1, 0.01, True, True, False, False, None),     # PS, 32 output channels
+    (1, 1, 64, 64, 21, 13, 1, None, True, False, False, False, 0.1),      # PS, 16 output channels (BW 16)
+    (3, 1, 96, 384, 9, 15, 1, 0.01, True, False, False, False, None),     # PS across two N tiles
+    (3, 1, 192, 192, 35, 41, 2, 0.2, False, True, False, True, None),     # streamed weights, M = 256 items
+    (7, 1, 64, 32, 37, 21, 1, 0.0, False, False, False, False, None),     # ragged 7x7
+    (3, 1, 32, 48, 18, 26, 1, None, False, True, False, False, 0.0),      # BN = 48 (BW 16)
 ]
 
 
@@ -187,7 +193,7 @@ def test_conv_tcgen05_engine(B16, case):
     res = torch.randn(oshape, generator=g).to(dev).to(bf) if use_res else None
     res2 = torch.randn(oshape, generator=g).to(dev).to(bf) if use_res2 else None
     scale = torch.rand((N, oshape[1]), generator=g).to(dev).contiguous() if use_scale else None
-    pc = B16.pack_conv(w, b)
+    pc = B16.pack_conv(w, b, ps=ps)
     assert pc.w_umma is not None
     xv = view_of(x.float(), dtype=bf, cs=Cin + 16, c0=8)
     rv = view_of(res.float(), dtype=bf, cs=oshape[1] + 8, c0=8) if use_res else None
@@ -399,7 +405,7 @@ def test_conv_tcgen05_padded_and_fp32_out(B16, case):
     oshape = (1, Cout // 4, 2 * H, 2 * W) if ps else (1, Cout, H, W)
     res = torch.randn(oshape, generator=g).to(dev) if use_res else None
     in_map = list(range(Cin)) + [-1] * (Cin_p - Cin) if Cin_p != Cin else None
-    pc = B16.pack_conv(w, b, in_map)
+    pc = B16.pack_conv(w, b, in_map, ps=ps)
     assert pc.w_umma is not None
     from vcm_ts_b200.backend import View
     xv = View(view_of(x.float(), dtype=bf, cs=Cin_p).t)      # all Cin_p channels; the pad is zero

@@ -54,10 +54,11 @@ def _code(dtype):
 
 class PackedConv:
     """Device-side packed weights of one nn.Conv2d (fp32 [tap][Cin_p][Cout] + optional UMMA bf16)."""
-    __slots__ = ("w", "bias", "K", "Cin", "Cout", "w_umma")
+    __slots__ = ("w", "bias", "K", "Cin", "Cout", "w_umma", "bias_tc", "ps")
 
     def __init__(self, w, bias, K, Cin, Cout, w_umma=None):
         self.w, self.bias, self.K, self.Cin, self.Cout, self.w_umma = w, bias, K, Cin, Cout, w_umma
+        self.bias_tc, self.ps = bias, False
 
 
 class CudaBackend:
@@ -92,7 +93,10 @@ class CudaBackend:
     def empty(self, shape, dtype):
         return torch.empty(shape, dtype=dtype, device=self.device)
 
-    def pack_conv(self, weight, bias, in_map=None, cin_p=None):
+    def pack_conv(self, weight, bias, in_map=None, cin_p=None, ps=False):
+        """ps: the conv is stored through PixelShuffle(2).  The tensor-core packing then orders the
+        GEMM columns position-major (c' = pos * Cout/4 + oc <- reference channel 4*oc + pos) so the
+        epilogue's channel blocks are contiguous output channels (tc_epilogue.cuh)."""
         Cout, Cin, K, _ = weight.shape
         w = weight.detach().to(self.device, torch.float32).contiguous()
         cin_p = cin_p or (len(in_map) if in_map is not None else Cin)
@@ -108,6 +112,12 @@ class CudaBackend:
             nbytes = self.L.vcm_conv2d_tc_weight_bytes(Cout, cin_p, K)
             if nbytes > 0:
                 wu = torch.empty((nbytes,), dtype=torch.uint8, device=self.device)
+                if ps:
+                    assert Cout % 4 == 0
+                    perm = torch.arange(Cout, device=self.device).reshape(Cout // 4, 4).t().reshape(-1)
+                    w = w[perm].contiguous()
+                    pc.bias_tc = pc.bias[perm].contiguous()
+                    pc.ps = True
                 check(self.L.vcm_pack_conv_weight_umma(w.data_ptr(), wu.data_ptr(), Cout, Cin, K, cin_p,
                                                        m.data_ptr() if m is not None else None,
                                                        self.stream), "vcm_pack_conv_weight_umma")
@@ -155,18 +165,19 @@ class CudaBackend:
                      out2.cs if slope2 is not None else 0, flags,
                      float(pre or 0.0), float(post or 0.0), float(slope2 or 0.0),
                      _code(x.dtype), _code(out.dtype))
-        args = (ctypes.byref(d), x.ptr, None, pc.bias.data_ptr(), res.ptr if res is not None else None,
+        args = [ctypes.byref(d), x.ptr, None, pc.bias.data_ptr(), res.ptr if res is not None else None,
                 res_scale.data_ptr() if res_scale is not None else None,
                 res2.ptr if res2 is not None else None, out.ptr,
-                out2.ptr if slope2 is not None else None, self.stream)
+                out2.ptr if slope2 is not None else None, self.stream]
         if pc.w_umma is not None and self.L.vcm_conv2d_tc_supported(ctypes.byref(d)) == 1:
-            a = list(args)
-            a[2] = pc.w_umma.data_ptr()
-            check(self.L.vcm_conv2d_tc_fwd(*a), "vcm_conv2d_tc_fwd")
+            if pc.ps != bool(ps):
+                raise RuntimeError("conv weights were packed for ps=%s but the conv is launched with ps=%s"
+                                   % (pc.ps, bool(ps)))
+            args[2], args[3] = pc.w_umma.data_ptr(), pc.bias_tc.data_ptr()
+            check(self.L.vcm_conv2d_tc_fwd(*args), "vcm_conv2d_tc_fwd")
         else:
-            a = list(args)
-            a[2] = pc.w.data_ptr()
-            check(self.L.vcm_conv2d_fwd(*a), "vcm_conv2d_fwd")
+            args[2] = pc.w.data_ptr()
+            check(self.L.vcm_conv2d_fwd(*args), "vcm_conv2d_fwd")
         self.launches += 1
         return (out, out2) if slope2 is not None else out
 

@@ -7,6 +7,8 @@
 // i.e. layers.py:42-127 (ResidualBlock*, subpel_conv), video_net.py:74-96 (ResBlock),
 // video_net.py:165-179 (ConvBlockResidual: up_dim(x) + conv(x)*se), video_model.py:40-68.
 #pragma once
+#include <stdlib.h>
+
 #include "common.cuh"
 
 struct ConvParams {
@@ -23,12 +25,13 @@ struct ConvParams {
   int flags;
   float pre_slope, post_slope, out2_slope;
   int cin_chunks, vecA, vecB, tiles_x, tiles_y;
+  int debug;   // VCM_TC_DEBUG bit mask (profiling experiments only; 0 in normal use)
 };
 
 template <typename T>
 __device__ __forceinline__ void conv_epilogue_store(const ConvParams& P, int n, int oy, int ox,
-                                                    int co, float v) {
-  v += __ldg(P.bias + co);
+                                                    int co, float v, float bias) {
+  v += bias;
   if (P.flags & VCM_CONV_POST_ACT) v = leaky(v, P.post_slope);
   int oc = co, y2 = oy, x2 = ox, Hout = P.Ho, Wout = P.Wo, Cres = P.Cout;
   if (P.flags & VCM_CONV_PIXEL_SHUFFLE) {
@@ -67,5 +70,9 @@ static inline int conv_fill_params(const vcm_conv_desc* d, ConvParams& P) {
   P.res_cs = d->res_cstride; P.res2_cs = d->res2_cstride; P.out2_cs = d->out2_cstride;
   P.flags = d->flags; P.pre_slope = d->pre_slope; P.post_slope = d->post_slope;
   P.out2_slope = d->out2_slope;
+  {
+    static const int dbg = getenv("VCM_TC_DEBUG") ? atoi(getenv("VCM_TC_DEBUG")) : 0;
+    P.debug = dbg;
+  }
   return 0;
 }

@@ -17,8 +17,10 @@
 //     M = 256 (two 8x16 halves, MH = 2) so each slab is used for twice the pixels.
 // Traffic per 3x3 64->64 tile drops from 216 KB to 23 KB.
 //
-// Roles (352 threads): warp 0 = activation TMA, warp 10 = weight TMA, warp 1 = MMA issue + TMEM,
-// warps 2-5 / 6-9 = two epilogue warpgroups (one per TMEM accumulator buffer), see tc_epilogue.cuh.
+// Roles (384 threads = 3 warpgroups): warpgroup 0 = warp 0 activation TMA, warp 1 MMA issue + TMEM,
+// warp 2 weight TMA, warp 3 idle (setmaxnreg.dec); warpgroups 1 / 2 (warps 4-7 / 8-11) = epilogue, one per
+// TMEM accumulator buffer (setmaxnreg.inc: no spills -- with 227 KB of shared memory carved out L1 is
+// tiny and every local-memory access stalls for an L2 round trip), see tc_epilogue.cuh.
 #include <mutex>
 
 #include "conv_common.cuh"
@@ -29,7 +31,7 @@ using namespace tc;
 namespace {
 
 constexpr int HTW = 8, HTH = 16;
-constexpr int H_THREADS = 352;
+constexpr int H_THREADS = 384;
 constexpr int H_MAX_A = 6, H_MAX_B = 12;
 
 struct HaloGeom {
@@ -39,6 +41,7 @@ struct HaloGeom {
   int hw, hh, mh;
   int tiles_x, tiles_y, n_tiles, num_items;
   int bn, cout_p, tmem_cols, scalar_epi;
+  int epi_base, bar_base, epi_bw;
   uint32_t idesc;
 };
 
@@ -52,8 +55,7 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
 
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
-  const int b_slots = G.resident ? G.ntaps * G.nchunks : G.b_stages;
-  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + G.b_base + (size_t)b_slots * G.b_slot_bytes);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + G.bar_base);
   uint64_t* afull = bars;
   uint64_t* aempty = afull + H_MAX_A;
   uint64_t* bfull = aempty + H_MAX_A;
@@ -80,6 +82,8 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
+  if (warp < 4) {
+  reg_dec<56>();
   if (warp == 0) {
     // ============================ activation producer: one halo box per (item, chunk) ==========
     if (lane == 0) {
@@ -98,7 +102,7 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         }
       }
     }
-  } else if (warp == 10) {
+  } else if (warp == 2) {
     // ============================ weight producer ==============================================
     if (lane == 0) {
       if (G.resident) {
@@ -123,78 +127,107 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       }
     }
   } else if (warp == 1) {
-    // ============================ MMA issuer (one thread) ======================================
-    if (lane == 0) {
-      int as = 0, bs = 0, acc = 0;
-      uint32_t aphase = 0, bphase = 0, acc_phase = 0;
-      if (G.resident) {
-        mbar_wait(&bfull[0], 0);
+    // ============================ MMA issue ====================================================
+    // The whole warp walks the (warp-uniform) loops and waits on the barriers; one elected lane
+    // issues tcgen05.mma / commit.  Descriptors are advanced by adding 16-byte units to the address
+    // field: tap (ky,kx) of the halo tile starts (ky*hw + kx) pixel rows further.
+    int as = 0, bs = 0, acc = 0;
+    uint32_t aphase = 0, bphase = 0, acc_phase = 0;
+    if (G.resident) {
+      mbar_wait(&bfull[0], 0);
+      tc_fence_after();
+    }
+    const uint64_t bdesc0 = make_smem_desc(smem_u32(smem + G.b_base), 8u * ROWB, LAYOUT);
+    const uint32_t bslot16 = (uint32_t)G.b_slot_bytes >> 4;
+    const uint32_t arow16 = ROWB >> 4;                       // one pixel to the right
+    const uint32_t aline16 = ((uint32_t)G.hw * ROWB) >> 4;   // one halo row down
+    const uint32_t ahalf16 = (uint32_t)HTH * aline16;        // second 128-pixel half (mh == 2)
+    const int K = P.K;
+    for (int item = blockIdx.x; item < G.num_items; item += gridDim.x) {
+      mbar_wait(&tempty[acc], acc_phase ^ 1u);
+      tc_fence_after();
+      const uint32_t d_tmem = tmem_base + (uint32_t)(acc * G.mh * G.bn);
+      uint32_t accum = 0;
+      for (int ch = 0; ch < G.nchunks; ++ch) {
+        mbar_wait(&afull[as], aphase);
         tc_fence_after();
-      }
-      const uint32_t b_region = smem_u32(smem + G.b_base);
-      for (int item = blockIdx.x; item < G.num_items; item += gridDim.x) {
-        mbar_wait(&tempty[acc], acc_phase ^ 1u);
-        tc_fence_after();
-        const uint32_t d_tmem = tmem_base + (uint32_t)(acc * G.mh * G.bn);
-        for (int ch = 0; ch < G.nchunks; ++ch) {
-          mbar_wait(&afull[as], aphase);
-          tc_fence_after();
-          const uint32_t a_base = smem_u32(smem + (size_t)as * G.a_stage_bytes);
-          for (int tap = 0; tap < G.ntaps; ++tap) {
-            const int ky = tap / P.K, kx = tap - ky * P.K;
-            uint32_t b_addr;
+        const uint64_t adesc0 = make_smem_desc(smem_u32(smem + (size_t)as * G.a_stage_bytes), sbo, LAYOUT);
+        uint32_t bslot = (uint32_t)ch;   // resident slab index = tap * nchunks + ch
+        for (int ky = 0; ky < K; ++ky) {
+          uint32_t aoff = (uint32_t)ky * aline16;
+          for (int kx = 0; kx < K; ++kx, aoff += arow16, bslot += (uint32_t)G.nchunks) {
+            uint64_t bdesc;
             if (G.resident) {
-              b_addr = b_region + (uint32_t)((tap * G.nchunks + ch) * G.b_slot_bytes);
+              bdesc = bdesc0 + (uint64_t)(bslot * bslot16);
             } else {
               mbar_wait(&bfull[bs], bphase);
               tc_fence_after();
-              b_addr = b_region + (uint32_t)(bs * G.b_slot_bytes);
+              bdesc = bdesc0 + (uint64_t)((uint32_t)bs * bslot16);
             }
-            const uint64_t bdesc = make_smem_desc(b_addr, 8u * ROWB, LAYOUT);
-            for (int h = 0; h < G.mh; ++h) {
-              const uint32_t a_addr = a_base + (uint32_t)(((ky + h * HTH) * G.hw + kx)) * ROWB;
-              const uint64_t adesc = make_smem_desc(a_addr, sbo, LAYOUT);
+            if (elect_one() && !((P.debug & 4) && accum)) {
+              const uint64_t adesc = adesc0 + (uint64_t)aoff;
 #pragma unroll
               for (int k = 0; k < KSTEPS; ++k)
-                umma_bf16(d_tmem + (uint32_t)(h * G.bn), adesc + (uint64_t)(2 * k), bdesc + (uint64_t)(2 * k),
-                          G.idesc, (ch > 0 || tap > 0 || k > 0) ? 1u : 0u);
+                umma_bf16(d_tmem, adesc + (uint64_t)(2 * k), bdesc + (uint64_t)(2 * k), G.idesc,
+                          (k > 0) ? 1u : accum);
+              if (G.mh == 2) {
+#pragma unroll
+                for (int k = 0; k < KSTEPS; ++k)
+                  umma_bf16(d_tmem + (uint32_t)G.bn, adesc + (uint64_t)(ahalf16 + 2 * k), bdesc + (uint64_t)(2 * k),
+                            G.idesc, (k > 0) ? 1u : accum);
+              }
+              if (!G.resident) umma_commit(&bempty[bs]);
             }
+            __syncwarp();
+            accum = 1u;
             if (!G.resident) {
-              umma_commit(&bempty[bs]);
               if (++bs == G.b_stages) { bs = 0; bphase ^= 1u; }
             }
           }
-          umma_commit(&aempty[as]);
-          if (++as == G.a_stages) { as = 0; aphase ^= 1u; }
         }
-        umma_commit(&tfull[acc]);
-        acc ^= 1;
-        if (acc == 0) acc_phase ^= 1u;
+        if (elect_one()) umma_commit(&aempty[as]);
+        __syncwarp();
+        if (++as == G.a_stages) { as = 0; aphase ^= 1u; }
       }
+      if (elect_one()) umma_commit(&tfull[acc]);
+      __syncwarp();
+      acc ^= 1;
+      if (acc == 0) acc_phase ^= 1u;
     }
+  }
   } else {
-    // ============ epilogue: warpgroup g (warps 2-5 / 6-9) owns accumulator buffer g ============
-    const int g = (warp - 2) >> 2;
-    const int q = warp & 3;
-    const int m = q * 32 + lane;
-    const int py = m / HTW, px = m % HTW;
+    reg_inc<224>();
+    // ============ epilogue: warpgroup g (warps 4-7 / 8-11) owns accumulator buffer g ===========
+    const int g = (warp - 4) >> 2;
+    const int q = warp & 3;   // TMEM lane quarter this warp may access
+    const uint32_t stage = smem_u32(smem + G.epi_base) + (uint32_t)((warp - 4) * EPI_STAGE_FLOATS * 4);
     uint32_t acc_phase = 0;
     int local = 0;
     for (int item = blockIdx.x; item < G.num_items; item += gridDim.x, ++local) {
       if ((local & 1) != g) continue;
       const int nt = item % G.n_tiles, sp = item / G.n_tiles;
       const int n = sp / sp_tiles, rem = sp - n * sp_tiles;
-      const int ox = (rem % G.tiles_x) * HTW + px;
+      const int ox0 = (rem % G.tiles_x) * HTW;
       const int cbase = nt * G.bn;
       for (int h = 0; h < G.mh; ++h) {
-        const int oy = (rem / G.tiles_x) * (HTH * G.mh) + h * HTH + py;
-        const bool valid = oy < P.Ho && ox < P.Wo;
+        const int oy0 = (rem / G.tiles_x) * (HTH * G.mh) + h * HTH;
         const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)((g * G.mh + h) * G.bn);
-        if (G.bn % 32 == 0) epilogue_tile<32, HaloGeom>(P, G, n, oy, ox, valid, cbase, taddr, &tfull[g], acc_phase);
-        else epilogue_tile<16, HaloGeom>(P, G, n, oy, ox, valid, cbase, taddr, &tfull[g], acc_phase);
+        uint64_t* wait = h == 0 ? &tfull[g] : nullptr;
+        uint64_t* release = h == G.mh - 1 ? &tempty[g] : nullptr;
+        if (G.scalar_epi == 0) {
+          if (G.epi_bw == 32)
+            epilogue_warp_vec<32, HTW>(P, G.bn, n, oy0, ox0, cbase, taddr, stage, q, lane, wait, acc_phase, release);
+          else
+            epilogue_warp_vec<16, HTW>(P, G.bn, n, oy0, ox0, cbase, taddr, stage, q, lane, wait, acc_phase, release);
+        } else {
+          const int m = q * 32 + lane;
+          const int oy = oy0 + m / HTW, ox = ox0 + m % HTW;
+          if (G.scalar_epi == 2)
+            epilogue_thread_scalar<float>(P, G.bn, n, oy, ox, cbase, taddr, wait, acc_phase, release);
+          else
+            epilogue_thread_scalar<bf>(P, G.bn, n, oy, ox, cbase, taddr, wait, acc_phase, release);
+        }
       }
-      tc_fence_before();
-      mbar_arrive(&tempty[g]);
       acc_phase ^= 1u;
     }
   }
@@ -228,9 +261,8 @@ int vcm_conv_halo_launch(const vcm_conv_desc* d, const ConvParams& P, const void
   G.b_bytes = G.bn * chunk * 2;
   G.b_slot_bytes = round_up(G.b_bytes, 1024);
   const int slabs = G.ntaps * G.nchunks;
-  const int budget = SMEM_LIMIT - 1024 - 1024;   // alignment slack + barriers
-  const bool vec = d->out_dtype == VCM_BF16 && d->Cout % 16 == 0;
-  G.scalar_epi = vec ? 0 : (d->out_dtype == VCM_F32 ? 2 : 1);
+  const int budget = SMEM_LIMIT - 1024 - 1024 - EPI_STAGE_BYTES;   // alignment slack, barriers, epilogue staging
+  G.scalar_epi = tc_epilogue_mode(d, P);
 
   auto a_stage = [&](int mh) { return round_up(G.hw * (HTH * mh + P.K - 1) * chunk * 2, 1024); };
   // resident weights if they leave room for >= 3 activation stages
@@ -265,6 +297,7 @@ int vcm_conv_halo_launch(const vcm_conv_desc* d, const ConvParams& P, const void
   if (cols > 512) return 3;
   G.tmem_cols = cols;
   G.idesc = make_idesc_bf16(128, G.bn);
+  G.epi_bw = tc_epilogue_bw(d, G.bn);
 
   CUtensorMap tmA, tmB;
   {
@@ -295,7 +328,9 @@ int vcm_conv_halo_launch(const vcm_conv_desc* d, const ConvParams& P, const void
     }
   }
   const int b_slots = G.resident ? slabs : G.b_stages;
-  int smem_bytes = G.b_base + b_slots * G.b_slot_bytes + 1024 + 1024;
+  G.epi_base = G.b_base + b_slots * G.b_slot_bytes;
+  G.bar_base = G.epi_base + EPI_STAGE_BYTES;
+  int smem_bytes = G.bar_base + 1024 + 1024;
   if (smem_bytes < 120 * 1024) smem_bytes = 120 * 1024;   // one CTA per SM (TMEM is per CTA)
   const int grid = G.num_items < num_sms() ? G.num_items : num_sms();
 #define LAUNCH_HALO(CH)                                                                                  \

@@ -146,7 +146,7 @@ __global__ void __launch_bounds__(256) conv_simt_kernel(const ConvParams P) {
 #pragma unroll
     for (int j = 0; j < TN; ++j) {
       const int co = n0 + cx * TN + j;
-      if (co < P.Cout) conv_epilogue_store<TO>(P, n, oy, ox, co, acc[i][j]);
+      if (co < P.Cout) conv_epilogue_store<TO>(P, n, oy, ox, co, acc[i][j], __ldg(P.bias + co));
     }
   }
 }

@@ -30,7 +30,7 @@ using namespace tc;
 namespace {
 
 constexpr int TH = 8, TW = 16;     // output tile: 8 rows x 16 cols = 128 GEMM rows
-constexpr int NUM_THREADS = 320;   // warp 0 TMA, warp 1 MMA + TMEM alloc, warps 2-5 / 6-9 epilogue
+constexpr int NUM_THREADS = 384;   // warp 0 TMA, warp 1 MMA + TMEM alloc, warps 2-3 idle, warps 4-7 / 8-11 epilogue
 constexpr int MAX_STAGES = 12;
 
 struct TcGeom {
@@ -39,7 +39,8 @@ struct TcGeom {
   int tiles_x, tiles_y, n_tiles, num_items;   // items = spatial tiles x N tiles
   int bn, cout_p;                             // N per MMA, padded Cout (rows per weight slab set)
   int tmem_cols;
-  int scalar_epi;                             // fp32 output or Cout % 16 != 0: per-element epilogue
+  int scalar_epi;                             // tc_epilogue_mode()
+  int epi_base, bar_base, epi_bw;
   uint32_t idesc;
 };
 
@@ -54,7 +55,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
 
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
-  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + (size_t)G.stages * G.stage_bytes);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + G.bar_base);
   uint64_t* full = bars;
   uint64_t* empty = bars + MAX_STAGES;
   uint64_t* tfull = bars + 2 * MAX_STAGES;
@@ -83,6 +84,8 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
+  if (warp < 4) {
+  reg_dec<56>();
   if (warp == 0) {
     // ================================ TMA producer (one thread) ================================
     if (lane == 0) {
@@ -108,19 +111,19 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       }
     }
   } else if (warp == 1) {
-    // ================================ MMA issuer (one thread) ==================================
-    if (lane == 0) {
-      int stage = 0;
-      uint32_t phase = 0;
-      int acc = 0;
-      uint32_t acc_phase = 0;
-      for (int item = blockIdx.x; item < G.num_items; item += gridDim.x) {
-        mbar_wait(&tempty[acc], acc_phase ^ 1u);
+    // ================================ MMA issue (warp-uniform loop, one elected lane) ==========
+    int stage = 0;
+    uint32_t phase = 0;
+    int acc = 0;
+    uint32_t acc_phase = 0;
+    for (int item = blockIdx.x; item < G.num_items; item += gridDim.x) {
+      mbar_wait(&tempty[acc], acc_phase ^ 1u);
+      tc_fence_after();
+      const uint32_t d_tmem = tmem_base + (uint32_t)(acc * G.bn);
+      for (int it = 0; it < G.kiters; ++it) {
+        mbar_wait(&full[stage], phase);
         tc_fence_after();
-        const uint32_t d_tmem = tmem_base + (uint32_t)(acc * G.bn);
-        for (int it = 0; it < G.kiters; ++it) {
-          mbar_wait(&full[stage], phase);
-          tc_fence_after();
+        if (elect_one()) {
           const uint32_t sa = smem_u32(smem + (size_t)stage * G.stage_bytes);
           const uint64_t adesc = make_smem_desc(sa, SBO, LAYOUT);
           const uint64_t bdesc = make_smem_desc(sa + G.b_off, SBO, LAYOUT);
@@ -131,33 +134,44 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                       (it > 0 || k > 0) ? 1u : 0u);
           }
           umma_commit(&empty[stage]);
-          if (++stage == G.stages) { stage = 0; phase ^= 1u; }
         }
-        umma_commit(&tfull[acc]);
-        acc ^= 1;
-        if (acc == 0) acc_phase ^= 1u;
+        __syncwarp();
+        if (++stage == G.stages) { stage = 0; phase ^= 1u; }
       }
+      if (elect_one()) umma_commit(&tfull[acc]);
+      __syncwarp();
+      acc ^= 1;
+      if (acc == 0) acc_phase ^= 1u;
     }
+  }
   } else {
-    // ============ epilogue: warpgroup g (warps 2-5 / 6-9) owns accumulator buffer g ============
-    const int g = (warp - 2) >> 2;
+    reg_inc<224>();
+    // ============ epilogue: warpgroup g (warps 4-7 / 8-11) owns accumulator buffer g ===========
+    const int g = (warp - 4) >> 2;
     const int q = warp & 3;  // TMEM lane quarter this warp may access
-    const int m = q * 32 + lane;
-    const int py = m / TW, px = m % TW;
+    const uint32_t stage = smem_u32(smem + G.epi_base) + (uint32_t)((warp - 4) * EPI_STAGE_FLOATS * 4);
     uint32_t acc_phase = 0;
     int local = 0;
     for (int item = blockIdx.x; item < G.num_items; item += gridDim.x, ++local) {
       if ((local & 1) != g) continue;
       const int nt = item % G.n_tiles, sp = item / G.n_tiles;
       const int n = sp / sp_tiles, rem = sp - n * sp_tiles;
-      const int oy = (rem / G.tiles_x) * TH + py, ox = (rem % G.tiles_x) * TW + px;
-      const bool valid = oy < P.Ho && ox < P.Wo;
+      const int oy0 = (rem / G.tiles_x) * TH, ox0 = (rem % G.tiles_x) * TW;
       const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(g * G.bn);
       const int cbase = nt * G.bn;
-      if (G.bn % 32 == 0) epilogue_tile<32, TcGeom>(P, G, n, oy, ox, valid, cbase, taddr, &tfull[g], acc_phase);
-      else epilogue_tile<16, TcGeom>(P, G, n, oy, ox, valid, cbase, taddr, &tfull[g], acc_phase);
-      tc_fence_before();
-      mbar_arrive(&tempty[g]);
+      if (G.scalar_epi == 0) {
+        if (G.epi_bw == 32)
+          epilogue_warp_vec<32, TW>(P, G.bn, n, oy0, ox0, cbase, taddr, stage, q, lane, &tfull[g], acc_phase, &tempty[g]);
+        else
+          epilogue_warp_vec<16, TW>(P, G.bn, n, oy0, ox0, cbase, taddr, stage, q, lane, &tfull[g], acc_phase, &tempty[g]);
+      } else {
+        const int m = q * 32 + lane;
+        const int oy = oy0 + m / TW, ox = ox0 + m % TW;
+        if (G.scalar_epi == 2)
+          epilogue_thread_scalar<float>(P, G.bn, n, oy, ox, cbase, taddr, &tfull[g], acc_phase, &tempty[g]);
+        else
+          epilogue_thread_scalar<bf>(P, G.bn, n, oy, ox, cbase, taddr, &tfull[g], acc_phase, &tempty[g]);
+      }
       acc_phase ^= 1u;
     }
   }
@@ -207,13 +221,6 @@ extern "C" int vcm_conv2d_tc_supported(const vcm_conv_desc* d) {
   if (d->Cin % 16 || d->Cout < 1 || d->Cout > 2048) return 0;
   if (d->flags & VCM_CONV_PRE_ACT) return 0;
   if (d->in_cstride % 8) return 0;
-  const bool vec = d->out_dtype == VCM_BF16 && d->Cout % 16 == 0;
-  if (vec) {
-    if (d->out_cstride % 4) return 0;
-    if ((d->flags & (VCM_CONV_RES | VCM_CONV_RES_SCALE)) && d->res_cstride % 4) return 0;
-    if ((d->flags & VCM_CONV_RES2) && d->res2_cstride % 4) return 0;
-    if ((d->flags & VCM_CONV_OUT2) && d->out2_cstride % 4) return 0;
-  }
   if ((d->flags & VCM_CONV_PIXEL_SHUFFLE) && d->Cout % 4) return 0;
   if (d->stride == 2 && ((d->H & 1) || (d->W & 1))) return 0;
   return 1;
@@ -253,12 +260,7 @@ extern "C" int vcm_conv2d_tc_fwd(const vcm_conv_desc* d, const void* x, const vo
   VCM_CHECK_ARG(!(P.flags & VCM_CONV_RES_SCALE) || res_scale, "RES_SCALE without scale");
   VCM_CHECK_ARG(!(P.flags & VCM_CONV_RES2) || res2, "RES2 without tensor");
   VCM_CHECK_ARG(!(P.flags & VCM_CONV_OUT2) || y2, "OUT2 without tensor");
-  const bool vec = d->out_dtype == VCM_BF16 && d->Cout % 16 == 0;
   VCM_CHECK_ARG(((uintptr_t)x & 15) == 0 && ((uintptr_t)w_umma & 15) == 0, "x / weights must be 16-byte aligned");
-  if (vec)
-    VCM_CHECK_ARG(((uintptr_t)y & 7) == 0 && ((uintptr_t)res & 7) == 0 && ((uintptr_t)res2 & 7) == 0 &&
-                      ((uintptr_t)y2 & 7) == 0 && ((uintptr_t)bias & 15) == 0 && ((uintptr_t)res_scale & 15) == 0,
-                  "output / residual views must be 8-byte aligned");
   P.x = x; P.bias = bias; P.res = res; P.res_scale = res_scale; P.res2 = res2; P.y = y; P.y2 = y2;
 
   // stride-1 shapes go to the halo-tile engine (conv_halo.cu) unless VCM_TC_PERTAP=1 forces this one
@@ -282,7 +284,7 @@ extern "C" int vcm_conv2d_tc_fwd(const vcm_conv_desc* d, const void* x, const vo
   G.b_bytes = G.bn * chunk * 2;
   G.b_off = round_up(G.a_bytes, 1024);
   G.stage_bytes = G.b_off + round_up(G.b_bytes, 1024);
-  int stages = (SMEM_LIMIT - 1024 - SMEM_BAR_BYTES) / G.stage_bytes;
+  int stages = (SMEM_LIMIT - 1024 - SMEM_BAR_BYTES - EPI_STAGE_BYTES) / G.stage_bytes;
   if (stages > MAX_STAGES) stages = MAX_STAGES;
   if (stages > G.kiters * 2) stages = G.kiters * 2 > 2 ? G.kiters * 2 : 2;
   VCM_CHECK_ARG(stages >= 2, "stage does not fit shared memory");
@@ -294,7 +296,10 @@ extern "C" int vcm_conv2d_tc_fwd(const vcm_conv_desc* d, const void* x, const vo
   while (cols < 2 * G.bn) cols <<= 1;
   G.tmem_cols = cols;
   G.idesc = make_idesc_bf16(128, G.bn);
-  G.scalar_epi = vec ? 0 : (d->out_dtype == VCM_F32 ? 2 : 1);
+  G.scalar_epi = tc_epilogue_mode(d, P);
+  G.epi_bw = tc_epilogue_bw(d, G.bn);
+  G.epi_base = G.stages * G.stage_bytes;
+  G.bar_base = G.epi_base + EPI_STAGE_BYTES;
 
   CUtensorMap tmA, tmB;
   {
@@ -324,7 +329,7 @@ extern "C" int vcm_conv2d_tc_fwd(const vcm_conv_desc* d, const void* x, const vo
       return 1;
     }
   }
-  int smem_bytes = G.stages * G.stage_bytes + 1024 + SMEM_BAR_BYTES;
+  int smem_bytes = G.bar_base + 1024 + SMEM_BAR_BYTES;
   if (smem_bytes < 120 * 1024) smem_bytes = 120 * 1024;  // one CTA per SM (TMEM is allocated per CTA)
   const int grid = G.num_items < num_sms() ? G.num_items : num_sms();
   cudaStream_t s = (cudaStream_t)stream;

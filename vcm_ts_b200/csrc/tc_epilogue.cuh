@@ -1,126 +1,46 @@
 // vcm_ts_b200/csrc/tc_epilogue.cuh -- TMEM -> registers -> fused conv epilogue, shared by the two
 // tcgen05 kernels (conv_tc.cu: per-tap TMA, conv_halo.cu: halo tile + resident weights).
+//
+// Vector path (bf16 output, Cout % 16 == 0, 16-byte aligned views).  tcgen05.ld hands every thread
+// ONE pixel (TMEM lane) and BW consecutive channels; written straight to NHWC global memory that is
+// 32 different 128-byte lines per warp instruction (ncu of the first engine: 32 sectors / request,
+// LSU wavefronts 44 % of peak with the tensor pipe at 10 %).  So every epilogue warp owns a
+// [32 pixel][BW channel] fp32 staging tile in shared memory (XOR-swizzled 16-byte chunks, bank
+// conflict free both ways): it drops the accumulators there, then re-reads them so that a lane
+// holds 8 consecutive channels of a pixel and the warp covers 32/UNITS whole pixels -- every global
+// access (residuals, SE-scaled residual, output, activated twin) is a 16-byte piece of a contiguous
+// BW*2-byte run per pixel.  Bias / activation / residual arithmetic happens in that second mapping,
+// in the same float-op order as conv_epilogue_store.
+//
+// PixelShuffle: the tensor-core weight packing orders the GEMM columns position-major
+// (column c' = pos * Cout/4 + oc, pos = 2*dy + dx; backend.py pack_conv), so one BW block is BW
+// consecutive output channels of ONE sub-pixel position and the store is the same contiguous run at
+// pixel (2*oy + dy, 2*ox + dx).
+//
+// Scalar path (fp32 output or Cout % 16 != 0: flow / RGB heads): per-element conv_epilogue_store.
 #pragma once
 #include "conv_common.cuh"
 #include "tc_ptx.cuh"
 
 namespace tc {
 
-// ---------------------------------------------------------------------------------- epilogue
 using bf = __nv_bfloat16;
 
-__device__ __forceinline__ void unpack4(const uint2 r, float* f) {
+__device__ __forceinline__ void unpack8(const uint4 r, float* f) {
   const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&r);
-  const float2 a = __bfloat1622float2(h[0]), b = __bfloat1622float2(h[1]);
-  f[0] = a.x; f[1] = a.y; f[2] = b.x; f[3] = b.y;
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const float2 a = __bfloat1622float2(h[i]);
+    f[2 * i] = a.x;
+    f[2 * i + 1] = a.y;
+  }
 }
-__device__ __forceinline__ uint2 pack4(const float* f) {
-  uint2 r;
+__device__ __forceinline__ uint4 pack8(const float* f) {
+  uint4 r;
   __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(&r);
-  h[0] = __floats2bfloat162_rn(f[0], f[1]);
-  h[1] = __floats2bfloat162_rn(f[2], f[3]);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) h[i] = __floats2bfloat162_rn(f[2 * i], f[2 * i + 1]);
   return r;
-}
-
-// Address (in bf16 elements from a view base) of the 4-channel unit `u` of the BW-wide channel
-// block starting at c0, for this thread's pixel.  Non-PS: unit u = channels c0+4u..c0+4u+3 of pixel
-// (oy,ox).  PS: units are grouped by sub-pixel position pos = u / (BW/16): 4 consecutive output
-// channels oc0 + 4*(u % (BW/16)) .. of pixel (2oy+dy, 2ox+dx).
-template <int BW>
-struct UnitAddr {
-  size_t pix[4];   // pixel index per sub-position (non-PS uses [0])
-  int ch0;         // first output channel of the block (oc0 for PS)
-  bool ps;
-  __device__ __forceinline__ void init(const ConvParams& P, int n, int oy, int ox, int c0) {
-    ps = P.flags & VCM_CONV_PIXEL_SHUFFLE;
-    if (!ps) {
-      pix[0] = ((size_t)n * P.Ho + oy) * P.Wo + ox;
-      ch0 = c0;
-    } else {
-#pragma unroll
-      for (int pos = 0; pos < 4; ++pos)
-        pix[pos] = ((size_t)n * (2 * P.Ho) + 2 * oy + (pos >> 1)) * (2 * P.Wo) + 2 * ox + (pos & 1);
-      ch0 = c0 >> 2;
-    }
-  }
-  __device__ __forceinline__ size_t off(int u, int cs) const {
-    if (!ps) return pix[0] * cs + ch0 + 4 * u;
-    constexpr int UPP = BW / 16;   // units per position
-    return pix[u / UPP] * cs + ch0 + 4 * (u % UPP);
-  }
-};
-
-// Loads the residual operands of one BW block (issued BEFORE the accumulator is awaited).
-template <int BW>
-__device__ __forceinline__ void epi_prefetch(const ConvParams& P, const UnitAddr<BW>& A, uint2 (&r1)[BW / 4],
-                                             uint2 (&r2)[BW / 4]) {
-  if (P.flags & (VCM_CONV_RES | VCM_CONV_RES_SCALE)) {
-#pragma unroll
-    for (int u = 0; u < BW / 4; ++u)
-      r1[u] = __ldg(reinterpret_cast<const uint2*>(reinterpret_cast<const bf*>(P.res) + A.off(u, P.res_cs)));
-  }
-  if (P.flags & VCM_CONV_RES2) {
-#pragma unroll
-    for (int u = 0; u < BW / 4; ++u)
-      r2[u] = __ldg(reinterpret_cast<const uint2*>(reinterpret_cast<const bf*>(P.res2) + A.off(u, P.res2_cs)));
-  }
-}
-
-// v[BW]: accumulators of channels c0..c0+BW-1 (GEMM column order).  Same op order as
-// conv_epilogue_store: bias -> act -> (+res | + res*scale) -> (+res2) -> store (-> twin).
-template <int BW>
-__device__ __forceinline__ void epi_finish(const ConvParams& P, const UnitAddr<BW>& A, int n, int c0, float* v,
-                                           const uint2 (&r1)[BW / 4], const uint2 (&r2)[BW / 4]) {
-#pragma unroll
-  for (int q = 0; q < BW / 4; ++q) {
-    const float4 b = __ldg(reinterpret_cast<const float4*>(P.bias + c0) + q);
-    v[4 * q] += b.x; v[4 * q + 1] += b.y; v[4 * q + 2] += b.z; v[4 * q + 3] += b.w;
-  }
-  if (P.flags & VCM_CONV_POST_ACT) {
-#pragma unroll
-    for (int i = 0; i < BW; ++i) v[i] = leaky(v[i], P.post_slope);
-  }
-  constexpr int UPP = BW / 16;
-#pragma unroll
-  for (int u = 0; u < BW / 4; ++u) {
-    float w[4];
-    int chan;   // first output channel of this unit (for the SE scale lookup)
-    if (!A.ps) {
-#pragma unroll
-      for (int i = 0; i < 4; ++i) w[i] = v[4 * u + i];
-      chan = c0 + 4 * u;
-    } else {
-      const int pos = u / UPP, k0 = 4 * (u % UPP);   // oc = ch0 + k0 + i  <-  co = c0 + 4*(k0+i) + pos
-#pragma unroll
-      for (int i = 0; i < 4; ++i) w[i] = v[4 * (k0 + i) + pos];
-      chan = A.ch0 + k0;
-    }
-    if (P.flags & (VCM_CONV_RES | VCM_CONV_RES_SCALE)) {
-      float r[4];
-      unpack4(r1[u], r);
-      if (P.flags & VCM_CONV_RES) {
-#pragma unroll
-        for (int i = 0; i < 4; ++i) w[i] = r[i] + w[i];
-      } else {
-        const int Cres = A.ps ? (P.Cout >> 2) : P.Cout;
-        const float4 s = __ldg(reinterpret_cast<const float4*>(P.res_scale + (size_t)n * Cres + chan));
-        w[0] = w[0] + __fmul_rn(r[0], s.x); w[1] = w[1] + __fmul_rn(r[1], s.y);
-        w[2] = w[2] + __fmul_rn(r[2], s.z); w[3] = w[3] + __fmul_rn(r[3], s.w);
-      }
-    }
-    if (P.flags & VCM_CONV_RES2) {
-      float r[4];
-      unpack4(r2[u], r);
-#pragma unroll
-      for (int i = 0; i < 4; ++i) w[i] = r[i] + w[i];
-    }
-    *reinterpret_cast<uint2*>(reinterpret_cast<bf*>(P.y) + A.off(u, P.out_cs)) = pack4(w);
-    if (P.flags & VCM_CONV_OUT2) {
-#pragma unroll
-      for (int i = 0; i < 4; ++i) w[i] = leaky(w[i], P.out2_slope);
-      *reinterpret_cast<uint2*>(reinterpret_cast<bf*>(P.y2) + A.off(u, P.out2_cs)) = pack4(w);
-    }
-  }
 }
 
 // TMEM -> registers for BW columns of this thread's lane (one wait for all loads)
@@ -139,50 +59,220 @@ __device__ __forceinline__ void tmem_load_block(uint32_t taddr, float* v) {
   asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
 }
 
-template <int BW, class GEO>
-__device__ __forceinline__ void epilogue_tile(const ConvParams& P, const GEO& G, int n, int oy, int ox,
-                                              bool valid, int cbase, uint32_t taddr, uint64_t* tfull,
-                                              uint32_t parity) {
-  // block 0 residuals go out before we wait for the MMAs of this tile
-  UnitAddr<BW> A;
-  uint2 r1[BW / 4], r2[BW / 4];
-  const bool vec = !G.scalar_epi;
-  if (valid && vec) {
-    A.init(P, n, oy, ox, cbase);
-    epi_prefetch<BW>(P, A, r1, r2);
+// ------------------------------------------------------------------------------- vector path
+constexpr int EPI_STAGE_FLOATS = 32 * 32;                       // per warp: [32 px][<=32 ch] fp32
+constexpr int EPI_STAGE_BYTES = 8 * EPI_STAGE_FLOATS * 4;       // 8 epilogue warps
+
+__device__ __forceinline__ float4 lds128(uint32_t saddr) {
+  float4 v;
+  asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(saddr));
+  return v;
+}
+__device__ __forceinline__ void sts128(uint32_t saddr, float a, float b, float c, float d) {
+  asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(saddr), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
+}
+
+template <int BW>
+__device__ __forceinline__ int stage_swz(int p) {
+  return BW == 32 ? (p & 7) : ((p >> 1) & 3);
+}
+
+// Per-lane coordinates of one BW block in the coalesced mapping: lane -> (pixel slot, 8-channel unit)
+template <int BW>
+struct BlockCoords {
+  static constexpr int UNITS = BW / 8;        // 16-byte units per pixel
+  static constexpr int PIXPER = 32 / UNITS;   // pixels per warp instruction
+  static constexpr int ITERS = UNITS;         // warp instructions per 32-pixel tile
+  size_t pix[ITERS];   // output pixel index (PixelShuffle-resolved)
+  uint32_t vmask;      // bit it: pixel inside the image
+  int ch;              // first of this lane's 8 output channels
+};
+
+// TWID: pixels per tile row; wq: TMEM lane quarter of the warp; (oy0, ox0): tile origin
+template <int BW, int TWID>
+__device__ __forceinline__ void block_coords(const ConvParams& P, int n, int oy0, int ox0, int wq, int lane,
+                                             int c0, BlockCoords<BW>& C) {
+  constexpr int UNITS = BlockCoords<BW>::UNITS, PIXPER = BlockCoords<BW>::PIXPER;
+  const int u = lane % UNITS;
+  int dy = 0, dx = 0, chd = c0;
+  const bool ps = P.flags & VCM_CONV_PIXEL_SHUFFLE;
+  if (ps) {
+    const int q4 = P.Cout >> 2;
+    const int pos = c0 / q4;
+    chd = c0 - pos * q4;
+    dy = pos >> 1;
+    dx = pos & 1;
   }
-  mbar_wait(tfull, parity);
-  tc_fence_after();
-  for (int cb = 0; cb < G.bn; cb += BW) {
-    float v[BW];
-    tmem_load_block<BW>(taddr + (uint32_t)cb, v);
-    if (!valid) continue;
-    if (vec) {
-      UnitAddr<BW> An;
-      uint2 n1[BW / 4], n2[BW / 4];
-      const bool more = cb + BW < G.bn;
-      if (more) {   // next block's residuals in flight while this block is finished
-        An.init(P, n, oy, ox, cbase + cb + BW);
-        epi_prefetch<BW>(P, An, n1, n2);
-      }
-      epi_finish<BW>(P, A, n, cbase + cb, v, r1, r2);
-      if (more) {
-        A = An;
+  C.ch = chd + 8 * u;
+  C.vmask = 0;
 #pragma unroll
-        for (int u = 0; u < BW / 4; ++u) { r1[u] = n1[u]; r2[u] = n2[u]; }
-      }
-    } else {
+  for (int it = 0; it < UNITS; ++it) {
+    const int m = wq * 32 + it * PIXPER + lane / UNITS;
+    const int oy = oy0 + m / TWID, ox = ox0 + m % TWID;
+    if (oy < P.Ho && ox < P.Wo) C.vmask |= 1u << it;
+    C.pix[it] = ps ? ((size_t)n * (2 * P.Ho) + 2 * oy + dy) * (size_t)(2 * P.Wo) + 2 * ox + dx
+                   : ((size_t)n * P.Ho + oy) * (size_t)P.Wo + ox;
+  }
+}
+
+template <int BW>
+__device__ __forceinline__ void block_prefetch(const ConvParams& P, const BlockCoords<BW>& C,
+                                               uint4 (&r1)[BW / 8], uint4 (&r2)[BW / 8]) {
+  if (P.flags & (VCM_CONV_RES | VCM_CONV_RES_SCALE)) {
 #pragma unroll
-      for (int i = 0; i < BW; ++i) {
-        const int co = cbase + cb + i;
-        if (co < P.Cout) {
-          if (G.scalar_epi == 2) conv_epilogue_store<float>(P, n, oy, ox, co, v[i]);
-          else conv_epilogue_store<bf>(P, n, oy, ox, co, v[i]);
-        }
+    for (int it = 0; it < BW / 8; ++it)
+      if (C.vmask >> it & 1u)
+        r1[it] = __ldg(reinterpret_cast<const uint4*>(reinterpret_cast<const bf*>(P.res) +
+                                                      C.pix[it] * P.res_cs + C.ch));
+  }
+  if (P.flags & VCM_CONV_RES2) {
+#pragma unroll
+    for (int it = 0; it < BW / 8; ++it)
+      if (C.vmask >> it & 1u)
+        r2[it] = __ldg(reinterpret_cast<const uint4*>(reinterpret_cast<const bf*>(P.res2) +
+                                                      C.pix[it] * P.res2_cs + C.ch));
+  }
+}
+
+// bias -> act -> (+res | + res*scale) -> (+res2) -> store (-> twin); c0 = GEMM column of the block
+template <int BW>
+__device__ __forceinline__ void block_finish(const ConvParams& P, uint32_t stage, int lane, int n, int c0,
+                                             const BlockCoords<BW>& C, const uint4 (&r1)[BW / 8],
+                                             const uint4 (&r2)[BW / 8]) {
+  constexpr int UNITS = BlockCoords<BW>::UNITS, PIXPER = BlockCoords<BW>::PIXPER;
+  const int u = lane % UNITS;
+  float b[8], s[8];
+  {
+    const float4 b0 = __ldg(reinterpret_cast<const float4*>(P.bias + c0 + 8 * u));
+    const float4 b1 = __ldg(reinterpret_cast<const float4*>(P.bias + c0 + 8 * u + 4));
+    b[0] = b0.x; b[1] = b0.y; b[2] = b0.z; b[3] = b0.w; b[4] = b1.x; b[5] = b1.y; b[6] = b1.z; b[7] = b1.w;
+  }
+  if (P.flags & VCM_CONV_RES_SCALE) {
+    const int Cres = (P.flags & VCM_CONV_PIXEL_SHUFFLE) ? (P.Cout >> 2) : P.Cout;
+    const float* sp = P.res_scale + (size_t)n * Cres + C.ch;
+    const float4 s0 = __ldg(reinterpret_cast<const float4*>(sp));
+    const float4 s1 = __ldg(reinterpret_cast<const float4*>(sp + 4));
+    s[0] = s0.x; s[1] = s0.y; s[2] = s0.z; s[3] = s0.w; s[4] = s1.x; s[5] = s1.y; s[6] = s1.z; s[7] = s1.w;
+  }
+#pragma unroll
+  for (int it = 0; it < UNITS; ++it) {
+    const int p = it * PIXPER + lane / UNITS;
+    const int sw = stage_swz<BW>(p);
+    const float4 a0 = lds128(stage + (uint32_t)(p * BW + 4 * ((2 * u) ^ sw)) * 4u);
+    const float4 a1 = lds128(stage + (uint32_t)(p * BW + 4 * ((2 * u + 1) ^ sw)) * 4u);
+    if (!(C.vmask >> it & 1u)) continue;
+    float w[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
+#pragma unroll
+    for (int i = 0; i < 8; ++i) w[i] += b[i];
+    if (P.flags & VCM_CONV_POST_ACT) {
+#pragma unroll
+      for (int i = 0; i < 8; ++i) w[i] = leaky(w[i], P.post_slope);
+    }
+    if (P.flags & (VCM_CONV_RES | VCM_CONV_RES_SCALE)) {
+      float r[8];
+      unpack8(r1[it], r);
+      if (P.flags & VCM_CONV_RES) {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) w[i] = r[i] + w[i];
+      } else {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) w[i] = w[i] + __fmul_rn(r[i], s[i]);
       }
+    }
+    if (P.flags & VCM_CONV_RES2) {
+      float r[8];
+      unpack8(r2[it], r);
+#pragma unroll
+      for (int i = 0; i < 8; ++i) w[i] = r[i] + w[i];
+    }
+    if (!(P.debug & 1)) *reinterpret_cast<uint4*>(reinterpret_cast<bf*>(P.y) + C.pix[it] * P.out_cs + C.ch) = pack8(w);
+    if (P.flags & VCM_CONV_OUT2) {
+#pragma unroll
+      for (int i = 0; i < 8; ++i) w[i] = leaky(w[i], P.out2_slope);
+      *reinterpret_cast<uint4*>(reinterpret_cast<bf*>(P.y2) + C.pix[it] * P.out2_cs + C.ch) = pack8(w);
     }
   }
 }
 
+// One warp, one 32-pixel x bn accumulator slab.  taddr: TMEM address of (lane quarter, first column).
+// stage: shared-window address of this warp's staging tile.
+// wait != nullptr: wait for the accumulator (after the first block's residuals are in flight).
+// release != nullptr: arrive on it as soon as the last TMEM read of the slab has completed.
+template <int BW, int TWID>
+__device__ __forceinline__ void epilogue_warp_vec(const ConvParams& P, int bn, int n, int oy0, int ox0,
+                                                  int cbase, uint32_t taddr, uint32_t stage, int wq, int lane,
+                                                  uint64_t* wait, uint32_t parity, uint64_t* release) {
+  BlockCoords<BW> C;
+  uint4 r1[BW / 8], r2[BW / 8];
+  block_coords<BW, TWID>(P, n, oy0, ox0, wq, lane, cbase, C);
+  block_prefetch<BW>(P, C, r1, r2);
+  if (wait) {
+    mbar_wait(wait, parity);
+    tc_fence_after();
+  }
+  for (int cb = 0; cb < bn; cb += BW) {
+    {
+      float v[BW];
+      tmem_load_block<BW>(taddr + (uint32_t)cb, v);
+      const int sw = stage_swz<BW>(lane);
+#pragma unroll
+      for (int j = 0; j < BW / 4; ++j)
+        sts128(stage + (uint32_t)(lane * BW + 4 * (j ^ sw)) * 4u, v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+    }
+    const bool more = cb + BW < bn;
+    if (!more && release) {
+      tc_fence_before();
+      mbar_arrive(release);
+    }
+    __syncwarp();
+    BlockCoords<BW> Cn;
+    uint4 n1[BW / 8], n2[BW / 8];
+    if (more) {   // next block's residuals in flight while this block is finished
+      block_coords<BW, TWID>(P, n, oy0, ox0, wq, lane, cbase + cb + BW, Cn);
+      block_prefetch<BW>(P, Cn, n1, n2);
+    }
+    if (!(P.debug & 2)) block_finish<BW>(P, stage, lane, n, cbase + cb, C, r1, r2);
+    __syncwarp();
+    if (more) {
+      C = Cn;
+#pragma unroll
+      for (int it = 0; it < BW / 8; ++it) { r1[it] = n1[it]; r2[it] = n2[it]; }
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------- scalar path
+// thread = pixel (oy, ox); loops over the bn columns of the slab
+template <class T>
+__device__ __forceinline__ void epilogue_thread_scalar(const ConvParams& P, int bn, int n, int oy, int ox,
+                                                       int cbase, uint32_t taddr, uint64_t* wait,
+                                                       uint32_t parity, uint64_t* release) {
+  const bool valid = oy < P.Ho && ox < P.Wo;
+  if (wait) {
+    mbar_wait(wait, parity);
+    tc_fence_after();
+  }
+  for (int cb = 0; cb < bn; cb += 16) {
+    float v[16];
+    tmem_load_block<16>(taddr + (uint32_t)cb, v);
+    if (cb + 16 >= bn && release) {
+      tc_fence_before();
+      mbar_arrive(release);
+    }
+    if (!valid) continue;
+#pragma unroll
+    for (int i = 0; i < 16; ++i) {
+      const int c = cbase + cb + i;
+      if (c < P.Cout) {
+        int co = c;   // position-major GEMM column -> reference channel 4*oc + pos
+        if (P.flags & VCM_CONV_PIXEL_SHUFFLE) {
+          const int q4 = P.Cout >> 2;
+          co = 4 * (c % q4) + c / q4;
+        }
+        conv_epilogue_store<T>(P, n, oy, ox, co, v[i], __ldg(P.bias + c));
+      }
+    }
+  }
+}
 
 }  // namespace tc

@@ -56,6 +56,32 @@ constexpr int SMEM_LIMIT = 227 * 1024;
 
 }  // namespace tc
 
+#include "conv_common.cuh"
+
+namespace tc {
+
+// 0 = vector epilogue (bf16 out, Cout % 16 == 0, every view 16-byte aligned), 1 = scalar bf16,
+// 2 = scalar fp32 (tc_epilogue.cuh)
+inline int tc_epilogue_mode(const vcm_conv_desc* d, const ConvParams& P) {
+  if (d->out_dtype == VCM_F32) return 2;
+  auto al = [](const void* p) { return ((uintptr_t)p & 15) == 0; };
+  bool vec = d->Cout % 16 == 0 && d->out_cstride % 8 == 0 && al(P.y) && al(P.bias);
+  if (d->flags & (VCM_CONV_RES | VCM_CONV_RES_SCALE)) vec = vec && d->res_cstride % 8 == 0 && al(P.res);
+  if (d->flags & VCM_CONV_RES_SCALE) vec = vec && al(P.res_scale);
+  if (d->flags & VCM_CONV_RES2) vec = vec && d->res2_cstride % 8 == 0 && al(P.res2);
+  if (d->flags & VCM_CONV_OUT2) vec = vec && d->out2_cstride % 8 == 0 && al(P.y2);
+  if (d->flags & VCM_CONV_PIXEL_SHUFFLE) vec = vec && (d->Cout / 4) % 16 == 0;
+  return vec ? 0 : 1;
+}
+// channels per epilogue block: 32 when the N tile (and a PixelShuffle position group) is a multiple
+inline int tc_epilogue_bw(const vcm_conv_desc* d, int bn) {
+  if (bn % 32) return 16;
+  if ((d->flags & VCM_CONV_PIXEL_SHUFFLE) && (d->Cout / 4) % 32) return 16;
+  return 32;
+}
+
+}  // namespace tc
+
 // stride-1 halo engine (conv_halo.cu); returns 0 ok, 1 error, 3 = shape not taken (use per-tap)
 struct ConvParams;
 int vcm_conv_halo_launch(const vcm_conv_desc* d, const ConvParams& P, const void* x, const void* w_umma,

@@ -118,18 +118,19 @@ class CompressionModel(nn.Module):
             else:
                 backend = CudaBackend(dev, self._precision)      # raises without a B200
             rt = _Runtime(backend)
-            rt.graph = Graph(backend, lambda n, m=None: self._packed(rt, n, m), lambda n: self._lin(rt, n))
+            rt.graph = Graph(backend, lambda n, m=None, ps=False: self._packed(rt, n, m, ps),
+                             lambda n: self._lin(rt, n))
             self._rt = rt
         return self._rt
 
-    def _packed(self, rt, name, in_map):
+    def _packed(self, rt, name, in_map, ps=False):
         w = self.get_parameter(name + ".weight")
         b = self.get_parameter(name + ".bias")
-        key = (name, tuple(in_map) if in_map is not None else None)
+        key = (name, tuple(in_map) if in_map is not None else None, ps)
         tag = (w._version, w.data_ptr(), b._version, b.data_ptr())
         hit = rt.packed.get(key)
         if hit is None or hit[0] != tag:
-            hit = (tag, rt.B.pack_conv(w, b, in_map))
+            hit = (tag, rt.B.pack_conv(w, b, in_map, ps=ps))
             rt.packed[key] = hit
         return hit[1]
 

@@ -16,14 +16,14 @@ F32 = torch.float32
 
 
 class Graph:
-    """Shared building blocks.  `B` is a backend, `pc(name, in_map=None)` returns packed conv weights,
+    """Shared building blocks.  `B` is a backend, `pc(name, in_map, ps)` returns packed conv weights,
     `lin(name)` a device fp32 tensor of a Linear weight."""
 
     def __init__(self, B, pc, lin):
         self.B, self.pc, self.lin = B, pc, lin
 
     def conv(self, name, x, in_map=None, **kw):
-        return self.B.conv(x, self.pc(name, in_map), **kw)
+        return self.B.conv(x, self.pc(name, in_map, bool(kw.get("ps", False))), **kw)
 
     def conv_t(self, name, x, slope2, out=None, out2=None, **kw):
         """Conv whose output feeds a ResBlock: returns (y, y_act).  y_act = leaky_relu(y, slope2)
