@@ -87,6 +87,13 @@ int vcm_umma_probe(int32_t start_row, int32_t sbo_bytes, int32_t use_base_offset
                    void* stream);
 /* issue-rate probe: `iters` back-to-back 128xNx16 bf16 MMAs; out[0] = SM cycles, out[1] = iters */
 int vcm_umma_rate(int32_t N, int32_t iters, long long* out, void* stream);
+/* same, with the A operand starting `start_row` 128-byte rows into the buffer and 8-row groups sbo_bytes apart */
+int vcm_umma_rate2(int32_t N, int32_t iters, int32_t start_row, int32_t sbo_bytes, long long* out,
+                   void* stream);
+/* TMA box-shape throughput probe: all SMs stream {64 ch, bw, bh} boxes of an NHWC bf16 [H][W][64] image
+ * through a `stages`-deep ring (each box as nsplit TMA ops); out[0] = cycles of CTA 0, out[1] = its boxes */
+int vcm_tma_probe(const void* img, int32_t H, int32_t W, int32_t bw, int32_t bh, int32_t stages,
+                  int32_t nsplit, long long* out, void* stream);
 
 /* ---- layout / elementwise glue ------------------------------------------------------- */
 /* NCHW fp32 -> NHWC view (dtype) ; callers' tensors are NCHW fp32 (video_coder.py:99-117)  */

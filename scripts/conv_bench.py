@@ -21,6 +21,7 @@ SHAPES = {
     "c64_64_full": (3, 1, 64, 64, 1088, 1920, True, False),
     "c64_64_full_nores": (3, 1, 64, 64, 1088, 1920, False, False),
     "k1_64_64_full_nores": (1, 1, 64, 64, 1088, 1920, False, False),
+    "c64_64_q": (3, 1, 64, 64, 272, 480, False, False),
     "c64_64_half": (3, 1, 64, 64, 544, 960, True, False),
     "c128_128_q": (3, 1, 128, 128, 272, 480, True, False),
     "c128_64_full": (3, 1, 128, 64, 1088, 1920, False, False),
@@ -37,6 +38,7 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--iters", type=int, default=20)
     ap.add_argument("--shapes", default="all")
+    ap.add_argument("--hot", action="store_true", help="single buffer set (L2-resident where it fits)")
     a = ap.parse_args()
     B = CudaBackend("cuda:0", "bf16")
     bf = torch.bfloat16
@@ -49,6 +51,8 @@ def main():
         pc = B.pack_conv(w.cuda(), torch.zeros(Cout).cuda(), ps=ps)
         nbuf = max(2, int(300e6 // (H * W * Cin * 2)) + 1)
         nbuf = min(nbuf, 8)
+        if a.hot:
+            nbuf = 1
         xs = [View(torch.randn((1, H, W, Cin), device="cuda").to(bf)) for _ in range(nbuf)]
         oc = Cout // 4 if ps else Cout
         oh, ow = (2 * H, 2 * W) if ps else (H // stride, W // stride)

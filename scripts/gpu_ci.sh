@@ -11,13 +11,13 @@ run() { # name timeout cmd...
 }
 STAGES=${STAGES:-"k_fp32 k_tc e2e_fp32 e2e_bf16 smoke bench"}
 for s in $STAGES; do case $s in
-  k_fp32) run k_fp32 600 python -m pytest tests/test_gpu_kernels.py -m gpu -q -k "fp32_engine or mixed or layout or se_layer or motion or dual_prior or round_and_bits" ;;
-  k_probe) run k_probe 300 python -m pytest tests/test_gpu_kernels.py -m gpu -q -s -k "probe" ;;
-  k_tc) run k_tc 600 python -m pytest tests/test_gpu_kernels.py -m gpu -q -k "tcgen05" ;;
-  e2e_fp32) run e2e_fp32 900 python -m pytest tests/test_gpu_e2e.py -m gpu -q -s -k "fp32 or batched" ;;
-  e2e_bf16) run e2e_bf16 600 python -m pytest tests/test_gpu_e2e.py -m gpu -q -s -k "bf16" ;;
-  smoke) run smoke 600 python -c "import __graft_entry__ as g; g.smoke()" ;;
-  bench) run bench 900 python bench.py --steps 1 --warmup 1 --gop 8 ;;
+  k_fp32) run k_fp32 150 python -m pytest tests/test_gpu_kernels.py -m gpu -q -k "fp32_engine or mixed or layout or se_layer or motion or dual_prior or round_and_bits" ;;
+  k_probe) run k_probe 100 python -m pytest tests/test_gpu_kernels.py -m gpu -q -s -k "probe" ;;
+  k_tc) run k_tc 150 python -m pytest tests/test_gpu_kernels.py -m gpu -q -k "tcgen05" ;;
+  e2e_fp32) run e2e_fp32 300 python -m pytest tests/test_gpu_e2e.py -m gpu -q -s -k "fp32 or batched" ;;
+  e2e_bf16) run e2e_bf16 200 python -m pytest tests/test_gpu_e2e.py -m gpu -q -s -k "bf16" ;;
+  smoke) run smoke 200 python -c "import __graft_entry__ as g; g.smoke()" ;;
+  bench) run bench 400 python bench.py --steps 1 --warmup 1 --gop 8 ;;
   bench_full) run bench_full 1200 python bench.py ;;
   all_gpu) run all_gpu 1500 python -m pytest tests -m gpu -x -q ;;
 esac; done

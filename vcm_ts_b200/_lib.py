@@ -46,6 +46,8 @@ _PROTOS = {
     "vcm_conv2d_tc_fwd": (c_int, [POINTER(ConvDesc), _P, _P, _P, _P, _P, _P, _P, _P, _P]),
     "vcm_umma_probe": (c_int, [c_int32, c_int32, c_int32, _P, _P]),
     "vcm_umma_rate": (c_int, [c_int32, c_int32, _P, _P]),
+    "vcm_umma_rate2": (c_int, [c_int32, c_int32, c_int32, c_int32, _P, _P]),
+    "vcm_tma_probe": (c_int, [_P, c_int32, c_int32, c_int32, c_int32, c_int32, c_int32, _P, _P]),
     "vcm_nchw_to_nhwc": (c_int, [_P, _P, c_int32, c_int32, c_int32, c_int32, c_int32, c_int32, _P]),
     "vcm_nhwc_to_nchw": (c_int, [_P, _P, c_int32, c_int32, c_int32, c_int32, c_int32, c_int32,
                                  c_int32, c_float, c_float, _P]),

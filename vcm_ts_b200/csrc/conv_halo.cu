@@ -45,6 +45,88 @@ struct HaloGeom {
   uint32_t idesc;
 };
 
+struct HaloBars {
+  uint64_t *afull, *aempty, *bfull, *bempty, *tfull, *tempty;
+};
+
+// MMA-issuing warp.  The profile of a runtime-parametrised tap loop showed this warp, not the tensor
+// pipe, pacing the kernel (~540 cycles per tap for 4 MMAs): so the tap loops are unrolled for the
+// filter size, every operand descriptor is `base + compile-time constant` (tap (ky,kx) of the halo
+// tile starts (ky*hw + kx) pixel rows further; the address field counts 16-byte units), and a whole
+// (item, Cin chunk) batch of K*K*KSTEPS*MH MMAs is issued by the elected lane without leaving the
+// single-thread region.  The other lanes only take part in the barrier waits.
+template <int CHUNK, int K, int MH, bool RESIDENT>
+__device__ __forceinline__ void mma_role(const HaloGeom& G, const HaloBars& B, uint32_t a_smem, uint32_t b_smem,
+                                         uint32_t tmem_base) {
+  constexpr uint32_t LAYOUT = CHUNK == 64 ? 2u : (CHUNK == 32 ? 4u : 6u);
+  constexpr uint32_t ROWB = CHUNK * 2u;
+  constexpr int KSTEPS = CHUNK / 16;
+  constexpr uint32_t HW = HTW + K - 1;
+  constexpr uint32_t AROW16 = ROWB >> 4;             // one pixel to the right
+  constexpr uint32_t ALINE16 = (HW * ROWB) >> 4;     // one halo row down
+  constexpr uint32_t AHALF16 = HTH * ALINE16;        // second 128-pixel half (MH == 2)
+  int as = 0, bs = 0, acc = 0;   // bs / bphase live in the elected lane only (always the same lane)
+  uint32_t aphase = 0, bphase = 0, acc_phase = 0;
+  if (RESIDENT) {
+    mbar_wait(&B.bfull[0], 0);
+    tc_fence_after();
+  }
+  const uint64_t bdesc0 = make_smem_desc(b_smem, 8u * ROWB, LAYOUT);
+  const uint32_t bslot16 = (uint32_t)G.b_slot_bytes >> 4;
+  const uint32_t btap16 = bslot16 * (uint32_t)G.nchunks;   // resident: slab index = tap * nchunks + ch
+  const uint32_t idesc = G.idesc;
+  const uint32_t bn = (uint32_t)G.bn;
+  for (int item = blockIdx.x; item < G.num_items; item += gridDim.x) {
+    mbar_wait(&B.tempty[acc], acc_phase ^ 1u);
+    tc_fence_after();
+    const uint32_t d_tmem = tmem_base + (uint32_t)acc * (uint32_t)MH * bn;
+    for (int ch = 0; ch < G.nchunks; ++ch) {
+      mbar_wait(&B.afull[as], aphase);
+      tc_fence_after();
+      if (elect_one()) {
+        const uint64_t adesc0 = make_smem_desc(a_smem + (uint32_t)as * (uint32_t)G.a_stage_bytes, HW * ROWB, LAYOUT);
+        const uint64_t bch = bdesc0 + (uint64_t)((uint32_t)ch * bslot16);
+#pragma unroll
+        for (int ky = 0; ky < K; ++ky) {
+#pragma unroll
+          for (int kx = 0; kx < K; ++kx) {
+            const int tap = ky * K + kx;
+            uint64_t bdesc;
+            if (RESIDENT) {
+              bdesc = bch + (uint64_t)((uint32_t)tap * btap16);
+            } else {
+              mbar_wait(&B.bfull[bs], bphase);
+              tc_fence_after();
+              bdesc = bdesc0 + (uint64_t)((uint32_t)bs * bslot16);
+            }
+            const uint64_t adesc = adesc0 + (uint64_t)(ky * ALINE16 + kx * AROW16);
+#pragma unroll
+            for (int k = 0; k < KSTEPS; ++k)
+              umma_bf16(d_tmem, adesc + (uint64_t)(2 * k), bdesc + (uint64_t)(2 * k), idesc,
+                        (tap > 0 || k > 0) ? 1u : (ch > 0 ? 1u : 0u));
+            if (MH == 2) {
+#pragma unroll
+              for (int k = 0; k < KSTEPS; ++k)
+                umma_bf16(d_tmem + bn, adesc + (uint64_t)(AHALF16 + 2 * k), bdesc + (uint64_t)(2 * k), idesc,
+                          (tap > 0 || k > 0) ? 1u : (ch > 0 ? 1u : 0u));
+            }
+            if (!RESIDENT) {
+              umma_commit(&B.bempty[bs]);
+              if (++bs == G.b_stages) { bs = 0; bphase ^= 1u; }
+            }
+          }
+        }
+        umma_commit(&B.aempty[as]);
+        if (ch == G.nchunks - 1) umma_commit(&B.tfull[acc]);
+      }
+      __syncwarp();
+      if (++as == G.a_stages) { as = 0; aphase ^= 1u; }
+    }
+    acc ^= 1;
+    if (acc == 0) acc_phase ^= 1u;
+  }
+}
+
 template <int CHUNK>
 __global__ void __launch_bounds__(H_THREADS, 1)
 conv_halo_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
@@ -83,7 +165,7 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   const uint32_t tmem_base = *tmem_slot;
 
   if (warp < 4) {
-  reg_dec<56>();
+  reg_dec<72>();
   if (warp == 0) {
     // ============================ activation producer: one halo box per (item, chunk) ==========
     if (lane == 0) {
@@ -128,75 +210,21 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     }
   } else if (warp == 1) {
     // ============================ MMA issue ====================================================
-    // The whole warp walks the (warp-uniform) loops and waits on the barriers; one elected lane
-    // issues tcgen05.mma / commit.  Descriptors are advanced by adding 16-byte units to the address
-    // field: tap (ky,kx) of the halo tile starts (ky*hw + kx) pixel rows further.
-    int as = 0, bs = 0, acc = 0;
-    uint32_t aphase = 0, bphase = 0, acc_phase = 0;
-    if (G.resident) {
-      mbar_wait(&bfull[0], 0);
-      tc_fence_after();
-    }
-    const uint64_t bdesc0 = make_smem_desc(smem_u32(smem + G.b_base), 8u * ROWB, LAYOUT);
-    const uint32_t bslot16 = (uint32_t)G.b_slot_bytes >> 4;
-    const uint32_t arow16 = ROWB >> 4;                       // one pixel to the right
-    const uint32_t aline16 = ((uint32_t)G.hw * ROWB) >> 4;   // one halo row down
-    const uint32_t ahalf16 = (uint32_t)HTH * aline16;        // second 128-pixel half (mh == 2)
-    const int K = P.K;
-    for (int item = blockIdx.x; item < G.num_items; item += gridDim.x) {
-      mbar_wait(&tempty[acc], acc_phase ^ 1u);
-      tc_fence_after();
-      const uint32_t d_tmem = tmem_base + (uint32_t)(acc * G.mh * G.bn);
-      uint32_t accum = 0;
-      for (int ch = 0; ch < G.nchunks; ++ch) {
-        mbar_wait(&afull[as], aphase);
-        tc_fence_after();
-        const uint64_t adesc0 = make_smem_desc(smem_u32(smem + (size_t)as * G.a_stage_bytes), sbo, LAYOUT);
-        uint32_t bslot = (uint32_t)ch;   // resident slab index = tap * nchunks + ch
-        for (int ky = 0; ky < K; ++ky) {
-          uint32_t aoff = (uint32_t)ky * aline16;
-          for (int kx = 0; kx < K; ++kx, aoff += arow16, bslot += (uint32_t)G.nchunks) {
-            uint64_t bdesc;
-            if (G.resident) {
-              bdesc = bdesc0 + (uint64_t)(bslot * bslot16);
-            } else {
-              mbar_wait(&bfull[bs], bphase);
-              tc_fence_after();
-              bdesc = bdesc0 + (uint64_t)((uint32_t)bs * bslot16);
-            }
-            if (elect_one() && !((P.debug & 4) && accum)) {
-              const uint64_t adesc = adesc0 + (uint64_t)aoff;
-#pragma unroll
-              for (int k = 0; k < KSTEPS; ++k)
-                umma_bf16(d_tmem, adesc + (uint64_t)(2 * k), bdesc + (uint64_t)(2 * k), G.idesc,
-                          (k > 0) ? 1u : accum);
-              if (G.mh == 2) {
-#pragma unroll
-                for (int k = 0; k < KSTEPS; ++k)
-                  umma_bf16(d_tmem + (uint32_t)G.bn, adesc + (uint64_t)(ahalf16 + 2 * k), bdesc + (uint64_t)(2 * k),
-                            G.idesc, (k > 0) ? 1u : accum);
-              }
-              if (!G.resident) umma_commit(&bempty[bs]);
-            }
-            __syncwarp();
-            accum = 1u;
-            if (!G.resident) {
-              if (++bs == G.b_stages) { bs = 0; bphase ^= 1u; }
-            }
-          }
-        }
-        if (elect_one()) umma_commit(&aempty[as]);
-        __syncwarp();
-        if (++as == G.a_stages) { as = 0; aphase ^= 1u; }
-      }
-      if (elect_one()) umma_commit(&tfull[acc]);
-      __syncwarp();
-      acc ^= 1;
-      if (acc == 0) acc_phase ^= 1u;
-    }
+    HaloBars B{afull, aempty, bfull, bempty, tfull, tempty};
+    const uint32_t a_smem = smem_u32(smem), b_smem = smem_u32(smem + G.b_base);
+#define HALO_MMA(KK)                                                                              \
+  do {                                                                                            \
+    if (G.resident) mma_role<CHUNK, KK, 1, true>(G, B, a_smem, b_smem, tmem_base);                 \
+    else if (G.mh == 1) mma_role<CHUNK, KK, 1, false>(G, B, a_smem, b_smem, tmem_base);            \
+    else mma_role<CHUNK, KK, 2, false>(G, B, a_smem, b_smem, tmem_base);                           \
+  } while (0)
+    if (P.K == 3) HALO_MMA(3);
+    else if (P.K == 1) HALO_MMA(1);
+    else HALO_MMA(7);
+#undef HALO_MMA
   }
   } else {
-    reg_inc<224>();
+    reg_inc<216>();
     // ============ epilogue: warpgroup g (warps 4-7 / 8-11) owns accumulator buffer g ===========
     const int g = (warp - 4) >> 2;
     const int q = warp & 3;   // TMEM lane quarter this warp may access

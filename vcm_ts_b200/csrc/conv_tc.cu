@@ -220,6 +220,9 @@ extern "C" int vcm_conv2d_tc_supported(const vcm_conv_desc* d) {
   if (!(d->stride == 1 || d->stride == 2)) return 0;
   if (d->Cin % 16 || d->Cout < 1 || d->Cout > 2048) return 0;
   if (d->flags & VCM_CONV_PRE_ACT) return 0;
+  // the epilogue computes leaky_relu as max(v, v*slope): exact for slopes in [0, 1]
+  if ((d->flags & VCM_CONV_POST_ACT) && !(d->post_slope >= 0.f && d->post_slope <= 1.f)) return 0;
+  if ((d->flags & VCM_CONV_OUT2) && !(d->out2_slope >= 0.f && d->out2_slope <= 1.f)) return 0;
   if (d->in_cstride % 8) return 0;
   if ((d->flags & VCM_CONV_PIXEL_SHUFFLE) && d->Cout % 4) return 0;
   if (d->stride == 2 && ((d->H & 1) || (d->W & 1))) return 0;

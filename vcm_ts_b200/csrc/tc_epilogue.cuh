@@ -9,7 +9,8 @@
 // conflict free both ways): it drops the accumulators there, then re-reads them so that a lane
 // holds 8 consecutive channels of a pixel and the warp covers 32/UNITS whole pixels -- every global
 // access (residuals, SE-scaled residual, output, activated twin) is a 16-byte piece of a contiguous
-// BW*2-byte run per pixel.  Bias / activation / residual arithmetic happens in that second mapping,
+// BW*2-byte run per pixel (per-instruction address steps are warp-uniform constants: the profile of
+// the first version was instruction-bound, ~1100 warp instructions per 128x64 tile, 21 % address math).  Bias / activation / residual arithmetic happens in that second mapping,
 // in the same float-op order as conv_epilogue_store.
 //
 // PixelShuffle: the tensor-core weight packing orders the GEMM columns position-major
@@ -77,122 +78,22 @@ __device__ __forceinline__ int stage_swz(int p) {
   return BW == 32 ? (p & 7) : ((p >> 1) & 3);
 }
 
-// Per-lane coordinates of one BW block in the coalesced mapping: lane -> (pixel slot, 8-channel unit)
-template <int BW>
-struct BlockCoords {
+// Coalesced mapping of one warp's 32-pixel x BW-channel block: lane -> (pixel slot l = lane / UNITS,
+// 8-channel unit u = lane % UNITS); warp instruction `it` covers pixels it*PIXPER .. +PIXPER-1 of the
+// warp's 32 (row-major in a TWID-wide tile), so the (row, col) step of every instruction is a
+// compile-time constant and all per-instruction address deltas are warp-uniform.
+template <int BW, int TWID>
+struct VecMap {
   static constexpr int UNITS = BW / 8;        // 16-byte units per pixel
   static constexpr int PIXPER = 32 / UNITS;   // pixels per warp instruction
-  static constexpr int ITERS = UNITS;         // warp instructions per 32-pixel tile
-  size_t pix[ITERS];   // output pixel index (PixelShuffle-resolved)
-  uint32_t vmask;      // bit it: pixel inside the image
-  int ch;              // first of this lane's 8 output channels
+  static constexpr int ITERS = UNITS;         // warp instructions per 32-pixel block
+  static_assert(PIXPER % TWID == 0 || TWID % PIXPER == 0, "tile width / block width mismatch");
+  __host__ __device__ static constexpr int drow(int it) { return (it * PIXPER) / TWID; }
+  __host__ __device__ static constexpr int dcol(int it) { return (it * PIXPER) % TWID; }
 };
 
-// TWID: pixels per tile row; wq: TMEM lane quarter of the warp; (oy0, ox0): tile origin
-template <int BW, int TWID>
-__device__ __forceinline__ void block_coords(const ConvParams& P, int n, int oy0, int ox0, int wq, int lane,
-                                             int c0, BlockCoords<BW>& C) {
-  constexpr int UNITS = BlockCoords<BW>::UNITS, PIXPER = BlockCoords<BW>::PIXPER;
-  const int u = lane % UNITS;
-  int dy = 0, dx = 0, chd = c0;
-  const bool ps = P.flags & VCM_CONV_PIXEL_SHUFFLE;
-  if (ps) {
-    const int q4 = P.Cout >> 2;
-    const int pos = c0 / q4;
-    chd = c0 - pos * q4;
-    dy = pos >> 1;
-    dx = pos & 1;
-  }
-  C.ch = chd + 8 * u;
-  C.vmask = 0;
-#pragma unroll
-  for (int it = 0; it < UNITS; ++it) {
-    const int m = wq * 32 + it * PIXPER + lane / UNITS;
-    const int oy = oy0 + m / TWID, ox = ox0 + m % TWID;
-    if (oy < P.Ho && ox < P.Wo) C.vmask |= 1u << it;
-    C.pix[it] = ps ? ((size_t)n * (2 * P.Ho) + 2 * oy + dy) * (size_t)(2 * P.Wo) + 2 * ox + dx
-                   : ((size_t)n * P.Ho + oy) * (size_t)P.Wo + ox;
-  }
-}
-
-template <int BW>
-__device__ __forceinline__ void block_prefetch(const ConvParams& P, const BlockCoords<BW>& C,
-                                               uint4 (&r1)[BW / 8], uint4 (&r2)[BW / 8]) {
-  if (P.flags & (VCM_CONV_RES | VCM_CONV_RES_SCALE)) {
-#pragma unroll
-    for (int it = 0; it < BW / 8; ++it)
-      if (C.vmask >> it & 1u)
-        r1[it] = __ldg(reinterpret_cast<const uint4*>(reinterpret_cast<const bf*>(P.res) +
-                                                      C.pix[it] * P.res_cs + C.ch));
-  }
-  if (P.flags & VCM_CONV_RES2) {
-#pragma unroll
-    for (int it = 0; it < BW / 8; ++it)
-      if (C.vmask >> it & 1u)
-        r2[it] = __ldg(reinterpret_cast<const uint4*>(reinterpret_cast<const bf*>(P.res2) +
-                                                      C.pix[it] * P.res2_cs + C.ch));
-  }
-}
-
-// bias -> act -> (+res | + res*scale) -> (+res2) -> store (-> twin); c0 = GEMM column of the block
-template <int BW>
-__device__ __forceinline__ void block_finish(const ConvParams& P, uint32_t stage, int lane, int n, int c0,
-                                             const BlockCoords<BW>& C, const uint4 (&r1)[BW / 8],
-                                             const uint4 (&r2)[BW / 8]) {
-  constexpr int UNITS = BlockCoords<BW>::UNITS, PIXPER = BlockCoords<BW>::PIXPER;
-  const int u = lane % UNITS;
-  float b[8], s[8];
-  {
-    const float4 b0 = __ldg(reinterpret_cast<const float4*>(P.bias + c0 + 8 * u));
-    const float4 b1 = __ldg(reinterpret_cast<const float4*>(P.bias + c0 + 8 * u + 4));
-    b[0] = b0.x; b[1] = b0.y; b[2] = b0.z; b[3] = b0.w; b[4] = b1.x; b[5] = b1.y; b[6] = b1.z; b[7] = b1.w;
-  }
-  if (P.flags & VCM_CONV_RES_SCALE) {
-    const int Cres = (P.flags & VCM_CONV_PIXEL_SHUFFLE) ? (P.Cout >> 2) : P.Cout;
-    const float* sp = P.res_scale + (size_t)n * Cres + C.ch;
-    const float4 s0 = __ldg(reinterpret_cast<const float4*>(sp));
-    const float4 s1 = __ldg(reinterpret_cast<const float4*>(sp + 4));
-    s[0] = s0.x; s[1] = s0.y; s[2] = s0.z; s[3] = s0.w; s[4] = s1.x; s[5] = s1.y; s[6] = s1.z; s[7] = s1.w;
-  }
-#pragma unroll
-  for (int it = 0; it < UNITS; ++it) {
-    const int p = it * PIXPER + lane / UNITS;
-    const int sw = stage_swz<BW>(p);
-    const float4 a0 = lds128(stage + (uint32_t)(p * BW + 4 * ((2 * u) ^ sw)) * 4u);
-    const float4 a1 = lds128(stage + (uint32_t)(p * BW + 4 * ((2 * u + 1) ^ sw)) * 4u);
-    if (!(C.vmask >> it & 1u)) continue;
-    float w[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
-#pragma unroll
-    for (int i = 0; i < 8; ++i) w[i] += b[i];
-    if (P.flags & VCM_CONV_POST_ACT) {
-#pragma unroll
-      for (int i = 0; i < 8; ++i) w[i] = leaky(w[i], P.post_slope);
-    }
-    if (P.flags & (VCM_CONV_RES | VCM_CONV_RES_SCALE)) {
-      float r[8];
-      unpack8(r1[it], r);
-      if (P.flags & VCM_CONV_RES) {
-#pragma unroll
-        for (int i = 0; i < 8; ++i) w[i] = r[i] + w[i];
-      } else {
-#pragma unroll
-        for (int i = 0; i < 8; ++i) w[i] = w[i] + __fmul_rn(r[i], s[i]);
-      }
-    }
-    if (P.flags & VCM_CONV_RES2) {
-      float r[8];
-      unpack8(r2[it], r);
-#pragma unroll
-      for (int i = 0; i < 8; ++i) w[i] = r[i] + w[i];
-    }
-    if (!(P.debug & 1)) *reinterpret_cast<uint4*>(reinterpret_cast<bf*>(P.y) + C.pix[it] * P.out_cs + C.ch) = pack8(w);
-    if (P.flags & VCM_CONV_OUT2) {
-#pragma unroll
-      for (int i = 0; i < 8; ++i) w[i] = leaky(w[i], P.out2_slope);
-      *reinterpret_cast<uint4*>(reinterpret_cast<bf*>(P.y2) + C.pix[it] * P.out2_cs + C.ch) = pack8(w);
-    }
-  }
-}
+// leaky_relu for slopes in [0, 1] (all the path uses): max(v, v*slope) == (v > 0 ? v : v*slope)
+__device__ __forceinline__ float leaky01(float v, float slope) { return fmaxf(v, v * slope); }
 
 // One warp, one 32-pixel x bn accumulator slab.  taddr: TMEM address of (lane quarter, first column).
 // stage: shared-window address of this warp's staging tile.
@@ -202,22 +103,73 @@ template <int BW, int TWID>
 __device__ __forceinline__ void epilogue_warp_vec(const ConvParams& P, int bn, int n, int oy0, int ox0,
                                                   int cbase, uint32_t taddr, uint32_t stage, int wq, int lane,
                                                   uint64_t* wait, uint32_t parity, uint64_t* release) {
-  BlockCoords<BW> C;
-  uint4 r1[BW / 8], r2[BW / 8];
-  block_coords<BW, TWID>(P, n, oy0, ox0, wq, lane, cbase, C);
-  block_prefetch<BW>(P, C, r1, r2);
+  using M = VecMap<BW, TWID>;
+  constexpr int UNITS = M::UNITS, ITERS = M::ITERS;
+  const int u = lane % UNITS, l = lane / UNITS;
+  const int oyb = oy0 + wq * (32 / TWID) + l / TWID, oxb = ox0 + l % TWID;
+  const bool ps = P.flags & VCM_CONV_PIXEL_SHUFFLE;
+  const int sx = ps ? 2 : 1;
+  const int Wout = sx * P.Wo, Hout = sx * P.Ho;
+  const int q4 = P.Cout >> 2;
+  const bool has_res = P.flags & (VCM_CONV_RES | VCM_CONV_RES_SCALE);
+  const bool has_res2 = P.flags & VCM_CONV_RES2;
+  const float slope = (P.flags & VCM_CONV_POST_ACT) ? P.post_slope : 1.0f;   // 1.0: identity, exact
+  uint32_t vmask = 0;
+#pragma unroll
+  for (int it = 0; it < ITERS; ++it)
+    if (oyb + M::drow(it) < P.Ho && oxb + M::dcol(it) < P.Wo) vmask |= 1u << it;
+  // output pixel index of this lane's first pixel (sub-pixel position added per block), and the
+  // warp-uniform pixel-index step of instruction `it`
+  const size_t pixb = ((size_t)n * Hout + (size_t)(sx * oyb)) * (size_t)Wout + (size_t)(sx * oxb);
+  uint32_t dpix[ITERS];
+#pragma unroll
+  for (int it = 0; it < ITERS; ++it) dpix[it] = (uint32_t)(sx * (M::drow(it) * Wout + M::dcol(it)));
+
+  // block-dependent part: first pixel index (PixelShuffle position) and this lane's first channel
+  auto block_pos = [&](int c0, size_t& pix0, int& ch) {
+    int chd = c0, dy = 0, dx = 0;
+    if (ps) {
+      const int pos = c0 / q4;
+      chd = c0 - pos * q4;
+      dy = pos >> 1;
+      dx = pos & 1;
+    }
+    pix0 = pixb + (size_t)(dy * Wout + dx);
+    ch = chd + 8 * u;
+  };
+  auto prefetch = [&](size_t pix0, int ch, uint4 (&r1)[ITERS], uint4 (&r2)[ITERS]) {
+    if (has_res) {
+      const bf* rp = reinterpret_cast<const bf*>(P.res) + pix0 * (size_t)P.res_cs + ch;
+#pragma unroll
+      for (int it = 0; it < ITERS; ++it)
+        if (vmask >> it & 1u) r1[it] = __ldg(reinterpret_cast<const uint4*>(rp + (size_t)dpix[it] * P.res_cs));
+    }
+    if (has_res2) {
+      const bf* rp = reinterpret_cast<const bf*>(P.res2) + pix0 * (size_t)P.res2_cs + ch;
+#pragma unroll
+      for (int it = 0; it < ITERS; ++it)
+        if (vmask >> it & 1u) r2[it] = __ldg(reinterpret_cast<const uint4*>(rp + (size_t)dpix[it] * P.res2_cs));
+    }
+  };
+
+  size_t pix0;
+  int ch;
+  uint4 r1[ITERS], r2[ITERS];
+  block_pos(cbase, pix0, ch);
+  prefetch(pix0, ch, r1, r2);
   if (wait) {
     mbar_wait(wait, parity);
     tc_fence_after();
   }
+  const int sw_st = stage_swz<BW>(lane);
+  const uint32_t st_row = stage + (uint32_t)(lane * BW) * 4u;
   for (int cb = 0; cb < bn; cb += BW) {
     {
       float v[BW];
       tmem_load_block<BW>(taddr + (uint32_t)cb, v);
-      const int sw = stage_swz<BW>(lane);
 #pragma unroll
       for (int j = 0; j < BW / 4; ++j)
-        sts128(stage + (uint32_t)(lane * BW + 4 * (j ^ sw)) * 4u, v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+        sts128(st_row + (uint32_t)(4 * (j ^ sw_st)) * 4u, v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
     }
     const bool more = cb + BW < bn;
     if (!more && release) {
@@ -225,18 +177,76 @@ __device__ __forceinline__ void epilogue_warp_vec(const ConvParams& P, int bn, i
       mbar_arrive(release);
     }
     __syncwarp();
-    BlockCoords<BW> Cn;
-    uint4 n1[BW / 8], n2[BW / 8];
-    if (more) {   // next block's residuals in flight while this block is finished
-      block_coords<BW, TWID>(P, n, oy0, ox0, wq, lane, cbase + cb + BW, Cn);
-      block_prefetch<BW>(P, Cn, n1, n2);
+    size_t pixn = 0;
+    int chn = 0;
+    uint4 n1[ITERS], n2[ITERS];
+    if (more && (has_res || has_res2)) {   // next block's residuals in flight while this one is finished
+      block_pos(cbase + cb + BW, pixn, chn);
+      prefetch(pixn, chn, n1, n2);
     }
-    if (!(P.debug & 2)) block_finish<BW>(P, stage, lane, n, cbase + cb, C, r1, r2);
+    // ---- finish this block in the coalesced mapping
+    {
+      const int c0 = cbase + cb;
+      float b[8], sc[8];
+      {
+        const float4 b0 = __ldg(reinterpret_cast<const float4*>(P.bias + c0 + 8 * u));
+        const float4 b1 = __ldg(reinterpret_cast<const float4*>(P.bias + c0 + 8 * u + 4));
+        b[0] = b0.x; b[1] = b0.y; b[2] = b0.z; b[3] = b0.w; b[4] = b1.x; b[5] = b1.y; b[6] = b1.z; b[7] = b1.w;
+      }
+      if (P.flags & VCM_CONV_RES_SCALE) {
+        const float* sp = P.res_scale + (size_t)n * (ps ? q4 : P.Cout) + ch;
+        const float4 s0 = __ldg(reinterpret_cast<const float4*>(sp));
+        const float4 s1 = __ldg(reinterpret_cast<const float4*>(sp + 4));
+        sc[0] = s0.x; sc[1] = s0.y; sc[2] = s0.z; sc[3] = s0.w; sc[4] = s1.x; sc[5] = s1.y; sc[6] = s1.z; sc[7] = s1.w;
+      }
+      bf* yp = reinterpret_cast<bf*>(P.y) + pix0 * (size_t)P.out_cs + ch;
+      bf* y2p = (P.flags & VCM_CONV_OUT2) ? reinterpret_cast<bf*>(P.y2) + pix0 * (size_t)P.out2_cs + ch : nullptr;
+#pragma unroll
+      for (int it = 0; it < ITERS; ++it) {
+        const int p = it * M::PIXPER + l;
+        const int sw = stage_swz<BW>(p);
+        const uint32_t row = stage + (uint32_t)(p * BW) * 4u;
+        const float4 a0 = lds128(row + (uint32_t)(4 * ((2 * u) ^ sw)) * 4u);
+        const float4 a1 = lds128(row + (uint32_t)(4 * ((2 * u + 1) ^ sw)) * 4u);
+        if (!(vmask >> it & 1u) || (P.debug & 2)) continue;
+        float w[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
+#pragma unroll
+        for (int i = 0; i < 8; ++i) w[i] = leaky01(w[i] + b[i], slope);
+        if (has_res) {
+          float r[8];
+          unpack8(r1[it], r);
+          if (P.flags & VCM_CONV_RES) {
+#pragma unroll
+            for (int i = 0; i < 8; ++i) w[i] = r[i] + w[i];
+          } else {
+#pragma unroll
+            for (int i = 0; i < 8; ++i) w[i] = w[i] + __fmul_rn(r[i], sc[i]);
+          }
+        }
+        if (has_res2) {
+          float r[8];
+          unpack8(r2[it], r);
+#pragma unroll
+          for (int i = 0; i < 8; ++i) w[i] = r[i] + w[i];
+        }
+        *reinterpret_cast<uint4*>(yp + (size_t)dpix[it] * P.out_cs) = pack8(w);
+        if (y2p) {
+#pragma unroll
+          for (int i = 0; i < 8; ++i) w[i] = leaky01(w[i], P.out2_slope);
+          *reinterpret_cast<uint4*>(y2p + (size_t)dpix[it] * P.out2_cs) = pack8(w);
+        }
+      }
+    }
     __syncwarp();
     if (more) {
-      C = Cn;
+      if (has_res || has_res2) {
+        pix0 = pixn;
+        ch = chn;
 #pragma unroll
-      for (int it = 0; it < BW / 8; ++it) { r1[it] = n1[it]; r2[it] = n2[it]; }
+        for (int it = 0; it < ITERS; ++it) { r1[it] = n1[it]; r2[it] = n2[it]; }
+      } else {
+        block_pos(cbase + cb + BW, pix0, ch);
+      }
     }
   }
 }

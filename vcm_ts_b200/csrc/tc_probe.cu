@@ -86,14 +86,15 @@ extern "C" int vcm_umma_probe(int32_t start_row, int32_t sbo_bytes, int32_t use_
 // ---- MMA issue-rate probe: `iters` back-to-back 128 x N x 16 bf16 MMAs on fixed smem operands, one
 // commit at the end; out[0] = SM cycles from first issue to completion, out[1] = iters.
 namespace {
-__global__ void __launch_bounds__(128, 1) umma_rate_kernel(int N, int iters, long long* __restrict__ out) {
+__global__ void __launch_bounds__(128, 1) umma_rate_kernel(int N, int iters, int start_row, int sbo,
+                                                           long long* __restrict__ out) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
-  uint8_t* sA = smem;                 // 128 x 128 B
-  uint8_t* sB = smem + 128 * 128;     // 256 x 128 B
+  uint8_t* sA = smem;                 // 384 x 128 B (room for halo-style start rows / group strides)
+  uint8_t* sB = smem + 384 * 128;     // 256 x 128 B
   uint64_t* bar = reinterpret_cast<uint64_t*>(sB + 256 * 128);
   uint32_t* slot = reinterpret_cast<uint32_t*>(bar + 1);
-  for (int i = threadIdx.x; i < (128 + 256) * 128 / 4; i += blockDim.x) reinterpret_cast<uint32_t*>(smem)[i] = 0;
+  for (int i = threadIdx.x; i < (384 + 256) * 128 / 4; i += blockDim.x) reinterpret_cast<uint32_t*>(smem)[i] = 0;
   if (threadIdx.x == 0) {
     mbar_init(bar, 1);
     fence_barrier_init();
@@ -105,7 +106,7 @@ __global__ void __launch_bounds__(128, 1) umma_rate_kernel(int N, int iters, lon
   tc_fence_after();
   const uint32_t tmem_base = *slot;
   if (threadIdx.x == 0) {
-    const uint64_t adesc = make_smem_desc(smem_u32(sA), 1024u, 2u);
+    const uint64_t adesc = make_smem_desc(smem_u32(sA) + (uint32_t)start_row * 128u, (uint32_t)sbo, 2u);
     const uint64_t bdesc = make_smem_desc(smem_u32(sB), 1024u, 2u);
     const uint32_t idesc = make_idesc_bf16(128, N);
     const long long t0 = clock64();
@@ -127,14 +128,89 @@ __global__ void __launch_bounds__(128, 1) umma_rate_kernel(int N, int iters, lon
 }  // namespace
 
 extern "C" int vcm_umma_rate(int32_t N, int32_t iters, long long* out, void* stream) {
+  return vcm_umma_rate2(N, iters, 0, 1024, out, stream);
+}
+
+extern "C" int vcm_umma_rate2(int32_t N, int32_t iters, int32_t start_row, int32_t sbo_bytes, long long* out,
+                              void* stream) {
   VCM_CHECK_ARG(out && N >= 16 && N <= 256 && N % 16 == 0 && iters > 0, "bad argument");
-  const int smem_bytes = (128 + 256) * 128 + 64 + 1024;
+  VCM_CHECK_ARG(start_row >= 0 && sbo_bytes % 128 == 0 && start_row * 128 + 15 * sbo_bytes + 1024 <= 384 * 128,
+                "A tile outside the probe buffer");
+  const int smem_bytes = (384 + 256) * 128 + 64 + 1024;
   static bool attr_set = false;
   if (!attr_set) {
     cudaFuncSetAttribute(umma_rate_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes);
     attr_set = true;
   }
-  umma_rate_kernel<<<1, 128, smem_bytes, (cudaStream_t)stream>>>(N, iters, out);
+  umma_rate_kernel<<<1, 128, smem_bytes, (cudaStream_t)stream>>>(N, iters, start_row, sbo_bytes, out);
+  VCM_CHECK_LAUNCH();
+  return 0;
+}
+
+// ---------------------------------------------------------------------------------- TMA box probe
+// Every CTA streams `iters` boxes {64 ch, bw, bh} (128B swizzle) of an NHWC bf16 image through a
+// `stages`-deep shared-memory ring, walking the image like the conv engines do (CTA-interleaved
+// tiles).  nsplit > 1 issues each box as nsplit TMA operations of bh/nsplit rows.  out[0] = cycles of
+// CTA 0, out[1] = boxes it loaded.
+#include "tc_host.cuh"
+namespace {
+__global__ void __launch_bounds__(64, 1)
+tma_probe_kernel(const __grid_constant__ CUtensorMap tm, int bw, int bh, int tiles_x, int n_tiles, int stages,
+                 int stage_bytes, int nsplit, long long* out) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  uint64_t* full = reinterpret_cast<uint64_t*>(smem + (size_t)stages * stage_bytes);
+  uint64_t* empty = full + 16;
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < stages; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
+    fence_barrier_init();
+  }
+  __syncthreads();
+  const long long t0 = clock64();
+  const int sub = bh / nsplit;
+  if (threadIdx.x == 0) {
+    int stage = 0; uint32_t phase = 0;
+    for (int t = blockIdx.x; t < n_tiles; t += gridDim.x) {
+      const int y0 = (t / tiles_x) * bh, x0 = (t % tiles_x) * bw;
+      mbar_wait(&empty[stage], phase ^ 1u);
+      mbar_expect_tx(&full[stage], (uint32_t)(bw * bh * 128));
+      for (int s = 0; s < nsplit; ++s)
+        tma_load_4d(smem_u32(smem + (size_t)stage * stage_bytes + (size_t)s * sub * bw * 128), &tm, &full[stage], 0,
+                    x0, y0 + s * sub, 0);
+      if (++stage == stages) { stage = 0; phase ^= 1u; }
+    }
+  } else if (threadIdx.x == 32) {
+    int stage = 0; uint32_t phase = 0; long long n = 0;
+    for (int t = blockIdx.x; t < n_tiles; t += gridDim.x, ++n) {
+      mbar_wait(&full[stage], phase);
+      mbar_arrive(&empty[stage]);
+      if (++stage == stages) { stage = 0; phase ^= 1u; }
+    }
+    if (blockIdx.x == 0) { out[0] = clock64() - t0; out[1] = n; }
+  }
+}
+}  // namespace
+
+extern "C" int vcm_tma_probe(const void* img, int32_t H, int32_t W, int32_t bw, int32_t bh, int32_t stages,
+                             int32_t nsplit, long long* out, void* stream) {
+  EncodeTiledFn enc = get_encode_fn();
+  VCM_CHECK_ARG(enc && img && out && bh % nsplit == 0 && stages >= 1 && stages <= 16, "bad argument");
+  CUtensorMap tm;
+  cuuint64_t dims[4] = {64, (cuuint64_t)W, (cuuint64_t)H, 1};
+  cuuint64_t strides[3] = {128, (cuuint64_t)W * 128, (cuuint64_t)H * W * 128};
+  cuuint32_t box[4] = {64, (cuuint32_t)bw, (cuuint32_t)(bh / nsplit), 1};
+  cuuint32_t estr[4] = {1, 1, 1, 1};
+  CUresult r = enc(&tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(img), dims, strides, box, estr,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  VCM_CHECK_ARG(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled failed");
+  const int stage_bytes = round_up(bw * bh * 128, 1024);
+  const int smem_bytes = stages * stage_bytes + 1024 + 512;
+  VCM_CHECK_ARG(smem_bytes <= SMEM_LIMIT, "ring does not fit shared memory");
+  cudaFuncSetAttribute(tma_probe_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT);
+  const int tiles_x = W / bw, n_tiles = tiles_x * (H / bh);
+  tma_probe_kernel<<<num_sms(), 64, smem_bytes, (cudaStream_t)stream>>>(tm, bw, bh, tiles_x, n_tiles, stages, stage_bytes,
+                                                                       nsplit, out);
   VCM_CHECK_LAUNCH();
   return 0;
 }
