@@ -209,6 +209,9 @@ def main():
     ap.add_argument("--precision", default=os.environ.get("VCM_B200_PRECISION", "bf16"))
     ap.add_argument("--impl", default="b200")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--seqs-per-gpu", type=int, default=2,
+                    help="independent sequences coded concurrently per GPU (own thread + CUDA stream each): "
+                         "while one sequence's symbols are in the host rANS coder the other's convs run")
     a = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -216,7 +219,7 @@ def main():
     gop = a.gop
     cfg = {"workload": f"DCVC-HEM GOP-{gop} 1080p (1920x1088 padded) sequence encode+decode per GPU: "
                        f"1 I-frame (IntraNoAR) + {gop - 1} P-frames (DMC), real rANS bitstreams",
-           "gop": gop, "sequences_per_gpu": 1, "precision": a.precision, "parallelism": f"seq-shard x{world}",
+           "gop": gop, "sequences_per_gpu": a.seqs_per_gpu, "precision": a.precision, "parallelism": f"seq-shard x{world}",
            "weights": "random init (reference init, conv x0.7)",
            "l2": "working set per frame >> 126 MB L2 (1080p activations), no explicit flush"}
     sd_p, sd_i = make_state_dicts(0)
@@ -253,16 +256,47 @@ def main():
     dev = torch.device(f"cuda:{local}")
     torch.cuda.set_device(dev)
     from vcm_ts_b200.models import DMC, IntraNoAR
-    dmc, intra = DMC(precision=a.precision).eval(), IntraNoAR(precision=a.precision).eval()
-    dmc.load_state_dict(sd_p)
-    intra.load_state_dict(sd_i)
-    dmc, intra = dmc.to(dev), intra.to(dev)
-    dmc.update(force=True)
-    intra.update(force=True)
+    S = max(1, a.seqs_per_gpu)
     q = 1.0
-    seq_host = synth_sequence(gop, rank).pin_memory()
-    seq_dev = seq_host.to(dev)
-    host_out = torch.empty((gop, 3, H, W), dtype=torch.float32).pin_memory()
+    # one model instance, CUDA stream and frame buffers per concurrently coded sequence
+    workers = []
+    for k in range(S):
+        dmc_k, intra_k = DMC(precision=a.precision).eval(), IntraNoAR(precision=a.precision).eval()
+        dmc_k.load_state_dict(sd_p)
+        intra_k.load_state_dict(sd_i)
+        dmc_k, intra_k = dmc_k.to(dev), intra_k.to(dev)
+        dmc_k.update(force=True)
+        intra_k.update(force=True)
+        sh = synth_sequence(gop, rank * S + k).pin_memory()
+        workers.append(dict(dmc=dmc_k, intra=intra_k, seq_host=sh, seq_dev=sh.to(dev),
+                            host_out=torch.empty((gop, 3, H, W), dtype=torch.float32).pin_memory(),
+                            stream=torch.cuda.Stream(dev), bits=0))
+    dmc, intra, seq_dev = workers[0]["dmc"], workers[0]["intra"], workers[0]["seq_dev"]
+
+    def run_all(fn):
+        """fn(worker) for every sequence, each in its own thread on its own stream."""
+        torch.cuda.synchronize()
+        errs = []
+
+        def body(w):
+            try:
+                torch.cuda.set_device(dev)
+                with torch.cuda.stream(w["stream"]):
+                    fn(w)
+                    w["stream"].synchronize()
+            except BaseException as e:   # noqa: BLE001
+                errs.append(e)
+        if S == 1:
+            body(workers[0])
+        else:
+            ts = [threading.Thread(target=body, args=(w,)) for w in workers]
+            for t in ts:
+                t.start()
+            for t in ts:
+                t.join()
+        if errs:
+            raise errs[0]
+        torch.cuda.synchronize()
 
     def barrier():
         torch.cuda.synchronize()
@@ -283,31 +317,43 @@ def main():
             dist.all_reduce(ms, op=dist.ReduceOp.MAX)
         return ms.item()
 
-    bits_box = [0]
+    def one_resident(w, n=None):
+        w["bits"], _ = code_gop(w["dmc"], w["intra"], w["seq_dev"], n or gop, q)
+
+    def one_e2e(w):
+        w["bits"], _ = code_gop(w["dmc"], w["intra"], w["seq_host"], gop, q, host_out=w["host_out"],
+                                pinned_in=True, dev=dev)
 
     def step_resident():
-        bits_box[0], _ = code_gop(dmc, intra, seq_dev, gop, q)
+        run_all(one_resident)
 
     def step_e2e():
-        bits_box[0], _ = code_gop(dmc, intra, seq_host, gop, q, host_out=host_out, pinned_in=True, dev=dev)
-        torch.cuda.synchronize()
+        run_all(one_e2e)
 
     # warm-up (>= 3 coded frames each through both models; W steps of a short GOP)
     for _ in range(max(a.warmup, 1)):
-        code_gop(dmc, intra, seq_dev, min(gop, 3), q)
-    B = dmc._rt.B
-    Bi = intra._rt.B
+        run_all(lambda w: one_resident(w, min(gop, 3)))
+    backends = [w[m]._rt.B for w in workers for m in ("dmc", "intra")]
     clocks = ClockSampler(local)
     clocks.start()
-    l0 = B.launches + Bi.launches
+    l0 = sum(b.launches for b in backends)
     ms_res = timed(step_resident, a.steps)
-    launches = B.launches + Bi.launches - l0
+    launches = sum(b.launches for b in backends) - l0
     ms_e2e = timed(step_e2e, a.steps)
     clk = clocks.stop()
-    frames_total = gop * a.steps * world
+    frames_total = gop * a.steps * world * S
     value = frames_total / (ms_res * 1e-3)
     e2e = frames_total / (ms_e2e * 1e-3)
-    bpp = bits_box[0] / float(gop * H * W)
+    bpp = workers[0]["bits"] / float(gop * H * W)
+    single = None
+    if S > 1 and rank == 0:
+        # latency view: ONE sequence alone on the GPU (GPU idles while its symbols are in the host coder)
+        n1 = min(gop, 8)
+        torch.cuda.synchronize()
+        t0 = time.time()
+        code_gop(dmc, intra, seq_dev, n1, q)
+        torch.cuda.synchronize()
+        single = n1 / (time.time() - t0)
 
     roof = None
     cpu = None
@@ -345,12 +391,12 @@ def main():
             cpu = {"value": gop / per_gop, "unit": "frames/s", "cores": threads, "kind": "port",
                    "sample": ob["sample"]}
     if rank == 0:
-        seq_bytes = gop * 3 * H * W * 4
+        seq_bytes = S * gop * 3 * H * W * 4
         print(json.dumps({
             "metric": METRIC, "value": value, "unit": "frames/s", "n_gpus": world, "steps": a.steps,
             "warmup": a.warmup, "ms_per_step": ms_res / a.steps, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "bf16" if a.precision == "bf16" else "f32", "data": "synthetic",
-            "config": cfg, "clocks": clk, "bpp": bpp,
+            "config": cfg, "clocks": clk, "bpp": bpp, "single_sequence_frames_per_s": single,
             "e2e": {"value": e2e, "unit": "frames/s", "h2d_bytes_per_step": seq_bytes,
                     "d2h_bytes_per_step": seq_bytes, "ms_per_step": ms_e2e / a.steps},
             "gpu_launches": launches, "roofline": roof, "cpu_baseline": cpu}))
