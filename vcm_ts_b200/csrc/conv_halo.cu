@@ -32,7 +32,7 @@ namespace {
 
 constexpr int HTW = 8, HTH = 16;
 constexpr int H_THREADS = 384;
-constexpr int H_MAX_A = 6, H_MAX_B = 12;
+constexpr int H_MAX_A = 6, H_MAX_B = 12, H_MAX_ACC = 4;
 
 struct HaloGeom {
   int nchunks, ntaps, a_stages, b_stages, resident;
@@ -41,7 +41,8 @@ struct HaloGeom {
   int hw, hh, mh;
   int tiles_x, tiles_y, n_tiles, num_items;
   int bn, cout_p, tmem_cols, scalar_epi;
-  int epi_base, bar_base, epi_bw;
+  int nacc;   // TMEM accumulator ring depth (2 or 4): lets the MMA warp run ahead of both epilogue warpgroups
+  int epi_base, bar_base, bias_base, epi_bw;
   uint32_t idesc;
 };
 
@@ -57,7 +58,7 @@ struct HaloBars {
 // single-thread region.  The other lanes only take part in the barrier waits.
 template <int CHUNK, int K, int MH, bool RESIDENT>
 __device__ __forceinline__ void mma_role(const HaloGeom& G, const HaloBars& B, uint32_t a_smem, uint32_t b_smem,
-                                         uint32_t tmem_base) {
+                                         uint32_t tmem_base, int dbg) {
   constexpr uint32_t LAYOUT = CHUNK == 64 ? 2u : (CHUNK == 32 ? 4u : 6u);
   constexpr uint32_t ROWB = CHUNK * 2u;
   constexpr int KSTEPS = CHUNK / 16;
@@ -102,8 +103,9 @@ __device__ __forceinline__ void mma_role(const HaloGeom& G, const HaloBars& B, u
             const uint64_t adesc = adesc0 + (uint64_t)(ky * ALINE16 + kx * AROW16);
 #pragma unroll
             for (int k = 0; k < KSTEPS; ++k)
-              umma_bf16(d_tmem, adesc + (uint64_t)(2 * k), bdesc + (uint64_t)(2 * k), idesc,
-                        (tap > 0 || k > 0) ? 1u : (ch > 0 ? 1u : 0u));
+              if (!(dbg & 4) || (tap == 0 && k == 0))
+                umma_bf16(d_tmem, adesc + (uint64_t)(2 * k), bdesc + (uint64_t)(2 * k), idesc,
+                          (tap > 0 || k > 0) ? 1u : (ch > 0 ? 1u : 0u));
             if (MH == 2) {
 #pragma unroll
               for (int k = 0; k < KSTEPS; ++k)
@@ -122,8 +124,7 @@ __device__ __forceinline__ void mma_role(const HaloGeom& G, const HaloBars& B, u
       __syncwarp();
       if (++as == G.a_stages) { as = 0; aphase ^= 1u; }
     }
-    acc ^= 1;
-    if (acc == 0) acc_phase ^= 1u;
+    if (++acc == G.nacc) { acc = 0; acc_phase ^= 1u; }
   }
 }
 
@@ -143,8 +144,8 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   uint64_t* bfull = aempty + H_MAX_A;
   uint64_t* bempty = bfull + H_MAX_B;
   uint64_t* tfull = bempty + H_MAX_B;
-  uint64_t* tempty = tfull + 2;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + 2);
+  uint64_t* tempty = tfull + H_MAX_ACC;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + H_MAX_ACC);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int sp_tiles = G.tiles_x * G.tiles_y;
@@ -155,14 +156,20 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     prefetch_tmap(&tmB);
     for (int s = 0; s < H_MAX_A; ++s) { mbar_init(&afull[s], 1); mbar_init(&aempty[s], 1); }
     for (int s = 0; s < H_MAX_B; ++s) { mbar_init(&bfull[s], 1); mbar_init(&bempty[s], 1); }
-    for (int a = 0; a < 2; ++a) { mbar_init(&tfull[a], 1); mbar_init(&tempty[a], 128); }
+    for (int a = 0; a < H_MAX_ACC; ++a) { mbar_init(&tfull[a], 1); mbar_init(&tempty[a], 4); }
     fence_barrier_init();
   }
   if (warp == 1) tmem_alloc(tmem_slot, (uint32_t)G.tmem_cols);
+  {   // bias vector -> shared memory (the vector epilogue reads it per channel block)
+    float* bs_ = reinterpret_cast<float*>(smem + G.bias_base);
+    const int nb = G.cout_p < EPI_BIAS_MAX ? G.cout_p : EPI_BIAS_MAX;
+    for (int i = threadIdx.x; i < nb; i += blockDim.x) bs_[i] = i < P.Cout ? __ldg(P.bias + i) : 0.f;
+  }
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  const uint32_t bias_smem = smem_u32(smem + G.bias_base);
 
   if (warp < 4) {
   reg_dec<72>();
@@ -214,9 +221,9 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     const uint32_t a_smem = smem_u32(smem), b_smem = smem_u32(smem + G.b_base);
 #define HALO_MMA(KK)                                                                              \
   do {                                                                                            \
-    if (G.resident) mma_role<CHUNK, KK, 1, true>(G, B, a_smem, b_smem, tmem_base);                 \
-    else if (G.mh == 1) mma_role<CHUNK, KK, 1, false>(G, B, a_smem, b_smem, tmem_base);            \
-    else mma_role<CHUNK, KK, 2, false>(G, B, a_smem, b_smem, tmem_base);                           \
+    if (G.resident) mma_role<CHUNK, KK, 1, true>(G, B, a_smem, b_smem, tmem_base, P.debug);                 \
+    else if (G.mh == 1) mma_role<CHUNK, KK, 1, false>(G, B, a_smem, b_smem, tmem_base, P.debug);            \
+    else mma_role<CHUNK, KK, 2, false>(G, B, a_smem, b_smem, tmem_base, P.debug);                           \
   } while (0)
     if (P.K == 3) HALO_MMA(3);
     else if (P.K == 1) HALO_MMA(1);
@@ -229,24 +236,25 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     const int g = (warp - 4) >> 2;
     const int q = warp & 3;   // TMEM lane quarter this warp may access
     const uint32_t stage = smem_u32(smem + G.epi_base) + (uint32_t)((warp - 4) * EPI_STAGE_FLOATS * 4);
-    uint32_t acc_phase = 0;
     int local = 0;
     for (int item = blockIdx.x; item < G.num_items; item += gridDim.x, ++local) {
       if ((local & 1) != g) continue;
+      const int ab = local % G.nacc;                          // accumulator buffer (its parity is g)
+      const uint32_t acc_phase = (uint32_t)(local / G.nacc) & 1u;
       const int nt = item % G.n_tiles, sp = item / G.n_tiles;
       const int n = sp / sp_tiles, rem = sp - n * sp_tiles;
       const int ox0 = (rem % G.tiles_x) * HTW;
       const int cbase = nt * G.bn;
       for (int h = 0; h < G.mh; ++h) {
         const int oy0 = (rem / G.tiles_x) * (HTH * G.mh) + h * HTH;
-        const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)((g * G.mh + h) * G.bn);
-        uint64_t* wait = h == 0 ? &tfull[g] : nullptr;
-        uint64_t* release = h == G.mh - 1 ? &tempty[g] : nullptr;
+        const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)((ab * G.mh + h) * G.bn);
+        uint64_t* wait = h == 0 ? &tfull[ab] : nullptr;
+        uint64_t* release = h == G.mh - 1 ? &tempty[ab] : nullptr;
         if (G.scalar_epi == 0) {
           if (G.epi_bw == 32)
-            epilogue_warp_vec<32, HTW>(P, G.bn, n, oy0, ox0, cbase, taddr, stage, q, lane, wait, acc_phase, release);
+            epilogue_warp_vec<32, HTW>(P, G.bn, n, oy0, ox0, cbase, taddr, stage, q, lane, wait, acc_phase, release, bias_smem);
           else
-            epilogue_warp_vec<16, HTW>(P, G.bn, n, oy0, ox0, cbase, taddr, stage, q, lane, wait, acc_phase, release);
+            epilogue_warp_vec<16, HTW>(P, G.bn, n, oy0, ox0, cbase, taddr, stage, q, lane, wait, acc_phase, release, bias_smem);
         } else {
           const int m = q * 32 + lane;
           const int oy = oy0 + m / HTW, ox = ox0 + m % HTW;
@@ -256,7 +264,6 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             epilogue_thread_scalar<bf>(P, G.bn, n, oy, ox, cbase, taddr, wait, acc_phase, release);
         }
       }
-      acc_phase ^= 1u;
     }
   }
 
@@ -289,7 +296,8 @@ int vcm_conv_halo_launch(const vcm_conv_desc* d, const ConvParams& P, const void
   G.b_bytes = G.bn * chunk * 2;
   G.b_slot_bytes = round_up(G.b_bytes, 1024);
   const int slabs = G.ntaps * G.nchunks;
-  const int budget = SMEM_LIMIT - 1024 - 1024 - EPI_STAGE_BYTES;   // alignment slack, barriers, epilogue staging
+  const int bias_bytes = round_up((G.cout_p < EPI_BIAS_MAX ? G.cout_p : EPI_BIAS_MAX) * 4, 128);
+  const int budget = SMEM_LIMIT - 1024 - 512 - bias_bytes - EPI_STAGE_BYTES;   // alignment slack, barriers, bias, staging
   G.scalar_epi = tc_epilogue_mode(d, P);
 
   auto a_stage = [&](int mh) { return round_up(G.hw * (HTH * mh + P.K - 1) * chunk * 2, 1024); };
@@ -320,8 +328,9 @@ int vcm_conv_halo_launch(const vcm_conv_desc* d, const ConvParams& P, const void
   G.tiles_x = cdiv(P.Wo, HTW);
   G.tiles_y = cdiv(P.Ho, HTH * G.mh);
   G.num_items = G.tiles_x * G.tiles_y * P.N * G.n_tiles;
+  G.nacc = 4 * G.mh * G.bn <= 512 ? 4 : 2;
   int cols = 32;
-  while (cols < 2 * G.mh * G.bn) cols <<= 1;
+  while (cols < G.nacc * G.mh * G.bn) cols <<= 1;
   if (cols > 512) return 3;
   G.tmem_cols = cols;
   G.idesc = make_idesc_bf16(128, G.bn);
@@ -358,7 +367,8 @@ int vcm_conv_halo_launch(const vcm_conv_desc* d, const ConvParams& P, const void
   const int b_slots = G.resident ? slabs : G.b_stages;
   G.epi_base = G.b_base + b_slots * G.b_slot_bytes;
   G.bar_base = G.epi_base + EPI_STAGE_BYTES;
-  int smem_bytes = G.bar_base + 1024 + 1024;
+  G.bias_base = G.bar_base + 512;
+  int smem_bytes = G.bias_base + bias_bytes + 1024;
   if (smem_bytes < 120 * 1024) smem_bytes = 120 * 1024;   // one CTA per SM (TMEM is per CTA)
   const int grid = G.num_items < num_sms() ? G.num_items : num_sms();
 #define LAUNCH_HALO(CH)                                                                                  \

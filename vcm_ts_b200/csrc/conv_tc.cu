@@ -40,7 +40,7 @@ struct TcGeom {
   int bn, cout_p;                             // N per MMA, padded Cout (rows per weight slab set)
   int tmem_cols;
   int scalar_epi;                             // tc_epilogue_mode()
-  int epi_base, bar_base, epi_bw;
+  int epi_base, bar_base, bias_base, epi_bw;
   uint32_t idesc;
 };
 
@@ -74,15 +74,21 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     }
     for (int a = 0; a < 2; ++a) {
       mbar_init(&tfull[a], 1);
-      mbar_init(&tempty[a], 128);
+      mbar_init(&tempty[a], 4);
     }
     fence_barrier_init();
   }
   if (warp == 1) tmem_alloc(tmem_slot, (uint32_t)G.tmem_cols);
+  {   // bias vector -> shared memory (the vector epilogue reads it per channel block)
+    float* bs_ = reinterpret_cast<float*>(smem + G.bias_base);
+    const int nb = G.cout_p < EPI_BIAS_MAX ? G.cout_p : EPI_BIAS_MAX;
+    for (int i = threadIdx.x; i < nb; i += blockDim.x) bs_[i] = i < P.Cout ? __ldg(P.bias + i) : 0.f;
+  }
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  const uint32_t bias_smem = smem_u32(smem + G.bias_base);
 
   if (warp < 4) {
   reg_dec<56>();
@@ -161,9 +167,9 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       const int cbase = nt * G.bn;
       if (G.scalar_epi == 0) {
         if (G.epi_bw == 32)
-          epilogue_warp_vec<32, TW>(P, G.bn, n, oy0, ox0, cbase, taddr, stage, q, lane, &tfull[g], acc_phase, &tempty[g]);
+          epilogue_warp_vec<32, TW>(P, G.bn, n, oy0, ox0, cbase, taddr, stage, q, lane, &tfull[g], acc_phase, &tempty[g], bias_smem);
         else
-          epilogue_warp_vec<16, TW>(P, G.bn, n, oy0, ox0, cbase, taddr, stage, q, lane, &tfull[g], acc_phase, &tempty[g]);
+          epilogue_warp_vec<16, TW>(P, G.bn, n, oy0, ox0, cbase, taddr, stage, q, lane, &tfull[g], acc_phase, &tempty[g], bias_smem);
       } else {
         const int m = q * 32 + lane;
         const int oy = oy0 + m / TW, ox = ox0 + m % TW;
@@ -287,7 +293,8 @@ extern "C" int vcm_conv2d_tc_fwd(const vcm_conv_desc* d, const void* x, const vo
   G.b_bytes = G.bn * chunk * 2;
   G.b_off = round_up(G.a_bytes, 1024);
   G.stage_bytes = G.b_off + round_up(G.b_bytes, 1024);
-  int stages = (SMEM_LIMIT - 1024 - SMEM_BAR_BYTES - EPI_STAGE_BYTES) / G.stage_bytes;
+  const int bias_bytes = round_up((G.cout_p < EPI_BIAS_MAX ? G.cout_p : EPI_BIAS_MAX) * 4, 128);
+  int stages = (SMEM_LIMIT - 1024 - SMEM_BAR_BYTES - bias_bytes - EPI_STAGE_BYTES) / G.stage_bytes;
   if (stages > MAX_STAGES) stages = MAX_STAGES;
   if (stages > G.kiters * 2) stages = G.kiters * 2 > 2 ? G.kiters * 2 : 2;
   VCM_CHECK_ARG(stages >= 2, "stage does not fit shared memory");
@@ -303,6 +310,7 @@ extern "C" int vcm_conv2d_tc_fwd(const vcm_conv_desc* d, const void* x, const vo
   G.epi_bw = tc_epilogue_bw(d, G.bn);
   G.epi_base = G.stages * G.stage_bytes;
   G.bar_base = G.epi_base + EPI_STAGE_BYTES;
+  G.bias_base = G.bar_base + SMEM_BAR_BYTES;
 
   CUtensorMap tmA, tmB;
   {
@@ -332,7 +340,7 @@ extern "C" int vcm_conv2d_tc_fwd(const vcm_conv_desc* d, const void* x, const vo
       return 1;
     }
   }
-  int smem_bytes = G.bar_base + 1024 + SMEM_BAR_BYTES;
+  int smem_bytes = G.bias_base + bias_bytes + 1024;
   if (smem_bytes < 120 * 1024) smem_bytes = 120 * 1024;  // one CTA per SM (TMEM is allocated per CTA)
   const int grid = G.num_items < num_sms() ? G.num_items : num_sms();
   cudaStream_t s = (cudaStream_t)stream;

@@ -59,10 +59,26 @@ __device__ __forceinline__ void tmem_load_block(uint32_t taddr, float* v) {
   }
   asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
 }
+// the same without the wait: the registers are valid only after tmem_load_wait()
+template <int BW>
+__device__ __forceinline__ void tmem_load_issue(uint32_t taddr, float* v) {
+#pragma unroll
+  for (int j = 0; j < BW / 16; ++j) {
+    uint32_t* r = reinterpret_cast<uint32_t*>(v) + 16 * j;
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
+        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+          "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+        : "r"(taddr + 16u * j));
+  }
+}
+__device__ __forceinline__ void tmem_load_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 
 // ------------------------------------------------------------------------------- vector path
 constexpr int EPI_STAGE_FLOATS = 32 * 32;                       // per warp: [32 px][<=32 ch] fp32
 constexpr int EPI_STAGE_BYTES = 8 * EPI_STAGE_FLOATS * 4;       // 8 epilogue warps
+constexpr int EPI_BIAS_MAX = 2048;                              // bias vector kept in shared memory (floats)
 
 __device__ __forceinline__ float4 lds128(uint32_t saddr) {
   float4 v;
@@ -102,7 +118,8 @@ __device__ __forceinline__ float leaky01(float v, float slope) { return fmaxf(v,
 template <int BW, int TWID>
 __device__ __forceinline__ void epilogue_warp_vec(const ConvParams& P, int bn, int n, int oy0, int ox0,
                                                   int cbase, uint32_t taddr, uint32_t stage, int wq, int lane,
-                                                  uint64_t* wait, uint32_t parity, uint64_t* release) {
+                                                  uint64_t* wait, uint32_t parity, uint64_t* release,
+                                                  uint32_t bias_smem) {
   using M = VecMap<BW, TWID>;
   constexpr int UNITS = M::UNITS, ITERS = M::ITERS;
   const int u = lane % UNITS, l = lane / UNITS;
@@ -137,13 +154,15 @@ __device__ __forceinline__ void epilogue_warp_vec(const ConvParams& P, int bn, i
     pix0 = pixb + (size_t)(dy * Wout + dx);
     ch = chd + 8 * u;
   };
-  auto prefetch = [&](size_t pix0, int ch, uint4 (&r1)[ITERS], uint4 (&r2)[ITERS]) {
+  auto prefetch1 = [&](size_t pix0, int ch, uint4 (&r1)[ITERS]) {
     if (has_res) {
       const bf* rp = reinterpret_cast<const bf*>(P.res) + pix0 * (size_t)P.res_cs + ch;
 #pragma unroll
       for (int it = 0; it < ITERS; ++it)
         if (vmask >> it & 1u) r1[it] = __ldg(reinterpret_cast<const uint4*>(rp + (size_t)dpix[it] * P.res_cs));
     }
+  };
+  auto prefetch2 = [&](size_t pix0, int ch, uint4 (&r2)[ITERS]) {
     if (has_res2) {
       const bf* rp = reinterpret_cast<const bf*>(P.res2) + pix0 * (size_t)P.res2_cs + ch;
 #pragma unroll
@@ -156,41 +175,53 @@ __device__ __forceinline__ void epilogue_warp_vec(const ConvParams& P, int bn, i
   int ch;
   uint4 r1[ITERS], r2[ITERS];
   block_pos(cbase, pix0, ch);
-  prefetch(pix0, ch, r1, r2);
+  prefetch1(pix0, ch, r1);
+  prefetch2(pix0, ch, r2);
   if (wait) {
     mbar_wait(wait, parity);
     tc_fence_after();
   }
   const int sw_st = stage_swz<BW>(lane);
   const uint32_t st_row = stage + (uint32_t)(lane * BW) * 4u;
+  float v[BW];
+  tmem_load_issue<BW>(taddr, v);
   for (int cb = 0; cb < bn; cb += BW) {
-    {
-      float v[BW];
-      tmem_load_block<BW>(taddr + (uint32_t)cb, v);
-#pragma unroll
-      for (int j = 0; j < BW / 4; ++j)
-        sts128(st_row + (uint32_t)(4 * (j ^ sw_st)) * 4u, v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
-    }
     const bool more = cb + BW < bn;
-    if (!more && release) {
+    tmem_load_wait();
+#pragma unroll
+    for (int j = 0; j < BW / 4; ++j)
+      sts128(st_row + (uint32_t)(4 * (j ^ sw_st)) * 4u, v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+    if (more) tmem_load_issue<BW>(taddr + (uint32_t)(cb + BW), v);   // in flight while this block is finished
+    __syncwarp();
+    if (!more && release && lane == 0) {   // one arrival per warp (barrier count = 4 warps)
       tc_fence_before();
       mbar_arrive(release);
     }
+    // the whole block in the coalesced mapping, then the staging tile is free again
+    float4 a0[ITERS], a1[ITERS];
+#pragma unroll
+    for (int it = 0; it < ITERS; ++it) {
+      const int p = it * M::PIXPER + l;
+      const int sw = stage_swz<BW>(p);
+      const uint32_t row = stage + (uint32_t)(p * BW) * 4u;
+      a0[it] = lds128(row + (uint32_t)(4 * ((2 * u) ^ sw)) * 4u);
+      a1[it] = lds128(row + (uint32_t)(4 * ((2 * u + 1) ^ sw)) * 4u);
+    }
+    const float4 b0 = lds128(bias_smem + (uint32_t)(cbase + cb + 8 * u) * 4u);
+    const float4 b1 = lds128(bias_smem + (uint32_t)(cbase + cb + 8 * u + 4) * 4u);
     __syncwarp();
     size_t pixn = 0;
     int chn = 0;
-    uint4 n1[ITERS], n2[ITERS];
+    uint4 n1[ITERS];   // first residual double-buffered; the (rare) second one is refetched after use
     if (more && (has_res || has_res2)) {   // next block's residuals in flight while this one is finished
       block_pos(cbase + cb + BW, pixn, chn);
-      prefetch(pixn, chn, n1, n2);
+      prefetch1(pixn, chn, n1);
     }
     // ---- finish this block in the coalesced mapping
     {
       const int c0 = cbase + cb;
       float b[8], sc[8];
       {
-        const float4 b0 = __ldg(reinterpret_cast<const float4*>(P.bias + c0 + 8 * u));
-        const float4 b1 = __ldg(reinterpret_cast<const float4*>(P.bias + c0 + 8 * u + 4));
         b[0] = b0.x; b[1] = b0.y; b[2] = b0.z; b[3] = b0.w; b[4] = b1.x; b[5] = b1.y; b[6] = b1.z; b[7] = b1.w;
       }
       if (P.flags & VCM_CONV_RES_SCALE) {
@@ -203,13 +234,8 @@ __device__ __forceinline__ void epilogue_warp_vec(const ConvParams& P, int bn, i
       bf* y2p = (P.flags & VCM_CONV_OUT2) ? reinterpret_cast<bf*>(P.y2) + pix0 * (size_t)P.out2_cs + ch : nullptr;
 #pragma unroll
       for (int it = 0; it < ITERS; ++it) {
-        const int p = it * M::PIXPER + l;
-        const int sw = stage_swz<BW>(p);
-        const uint32_t row = stage + (uint32_t)(p * BW) * 4u;
-        const float4 a0 = lds128(row + (uint32_t)(4 * ((2 * u) ^ sw)) * 4u);
-        const float4 a1 = lds128(row + (uint32_t)(4 * ((2 * u + 1) ^ sw)) * 4u);
-        if (!(vmask >> it & 1u) || (P.debug & 2)) continue;
-        float w[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
+        if (!(vmask >> it & 1u)) continue;
+        float w[8] = {a0[it].x, a0[it].y, a0[it].z, a0[it].w, a1[it].x, a1[it].y, a1[it].z, a1[it].w};
 #pragma unroll
         for (int i = 0; i < 8; ++i) w[i] = leaky01(w[i] + b[i], slope);
         if (has_res) {
@@ -237,13 +263,13 @@ __device__ __forceinline__ void epilogue_warp_vec(const ConvParams& P, int bn, i
         }
       }
     }
-    __syncwarp();
     if (more) {
       if (has_res || has_res2) {
         pix0 = pixn;
         ch = chn;
 #pragma unroll
-        for (int it = 0; it < ITERS; ++it) { r1[it] = n1[it]; r2[it] = n2[it]; }
+        for (int it = 0; it < ITERS; ++it) r1[it] = n1[it];
+        prefetch2(pix0, ch, r2);
       } else {
         block_pos(cbase + cb + BW, pix0, ch);
       }
@@ -265,9 +291,10 @@ __device__ __forceinline__ void epilogue_thread_scalar(const ConvParams& P, int 
   for (int cb = 0; cb < bn; cb += 16) {
     float v[16];
     tmem_load_block<16>(taddr + (uint32_t)cb, v);
-    if (cb + 16 >= bn && release) {
+    if (cb + 16 >= bn && release) {   // one arrival per warp
       tc_fence_before();
-      mbar_arrive(release);
+      __syncwarp();
+      if ((threadIdx.x & 31) == 0) mbar_arrive(release);
     }
     if (!valid) continue;
 #pragma unroll
