@@ -259,6 +259,8 @@ def main():
     S = max(1, a.seqs_per_gpu)
     q = 1.0
     # one model instance, CUDA stream and frame buffers per concurrently coded sequence
+    from vcm_ts_b200 import sharding
+    my_units = sharding.assign_units(world * S, world, rank)   # independent sequences, round-robin over ranks
     workers = []
     for k in range(S):
         dmc_k, intra_k = DMC(precision=a.precision).eval(), IntraNoAR(precision=a.precision).eval()
@@ -267,7 +269,7 @@ def main():
         dmc_k, intra_k = dmc_k.to(dev), intra_k.to(dev)
         dmc_k.update(force=True)
         intra_k.update(force=True)
-        sh = synth_sequence(gop, rank * S + k).pin_memory()
+        sh = synth_sequence(gop, my_units[k]).pin_memory()
         workers.append(dict(dmc=dmc_k, intra=intra_k, seq_host=sh, seq_dev=sh.to(dev),
                             host_out=torch.empty((gop, 3, H, W), dtype=torch.float32).pin_memory(),
                             stream=torch.cuda.Stream(dev), bits=0))
@@ -372,7 +374,7 @@ def main():
         peak = peaks.get("bf16_tflops_sustained", 1400.0)
         use_tc = rf["tc_s"] > 0
         ach = (rf["tc_flop"] / rf["tc_s"] if use_tc else rf["all_flop"] / max(rf["all_s"], 1e-9)) / 1e12
-        roof = {"bound": "tensor", "kernel": "conv_tc_kernel (tcgen05 implicit GEMM)" if use_tc else "conv_simt_kernel",
+        roof = {"bound": "tensor", "kernel": "conv_halo_kernel / conv_tc_kernel (tcgen05 implicit GEMM, all launches of one P-frame)" if use_tc else "conv_simt_kernel",
                 "achieved": ach, "peak": peak, "unit": "TFLOP/s", "frac": ach / peak,
                 "peak_source": "MEASURED_PEAKS.json bf16_tflops_sustained" if peaks else "fallback 1400 (sustained)",
                 "traffic": None,
