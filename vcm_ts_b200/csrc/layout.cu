@@ -101,6 +101,36 @@ __global__ void maxpool2_kernel(const T* __restrict__ src, T* __restrict__ dst, 
   }
 }
 
+// bf16, 8 channels (16 bytes) per thread
+__global__ void maxpool2_bf16x8_kernel(const __nv_bfloat16* __restrict__ src, __nv_bfloat16* __restrict__ dst,
+                                       int N, int H, int W, int C, int src_cs, int dst_cs) {
+  const int Ho = H / 2, Wo = W / 2, G = C / 8;
+  const int64_t total = (int64_t)N * Ho * Wo * G;
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total;
+       i += (int64_t)gridDim.x * blockDim.x) {
+    const int g = (int)(i % G);
+    int64_t p = i / G;
+    const int ox = (int)(p % Wo);
+    p /= Wo;
+    const int oy = (int)(p % Ho);
+    const int n = (int)(p / Ho);
+    const __nv_bfloat16* s = src + (((int64_t)n * H + 2 * oy) * W + 2 * ox) * src_cs + g * 8;
+    const uint4 a = __ldg(reinterpret_cast<const uint4*>(s));
+    const uint4 b = __ldg(reinterpret_cast<const uint4*>(s + src_cs));
+    const uint4 e = __ldg(reinterpret_cast<const uint4*>(s + (int64_t)W * src_cs));
+    const uint4 f = __ldg(reinterpret_cast<const uint4*>(s + (int64_t)(W + 1) * src_cs));
+    const __nv_bfloat162* ha = reinterpret_cast<const __nv_bfloat162*>(&a);
+    const __nv_bfloat162* hb = reinterpret_cast<const __nv_bfloat162*>(&b);
+    const __nv_bfloat162* he = reinterpret_cast<const __nv_bfloat162*>(&e);
+    const __nv_bfloat162* hf = reinterpret_cast<const __nv_bfloat162*>(&f);
+    uint4 r;
+    __nv_bfloat162* hr = reinterpret_cast<__nv_bfloat162*>(&r);
+#pragma unroll
+    for (int k = 0; k < 4; ++k) hr[k] = __hmax2(__hmax2(ha[k], hb[k]), __hmax2(he[k], hf[k]));
+    *reinterpret_cast<uint4*>(dst + (((int64_t)n * Ho + oy) * Wo + ox) * dst_cs + g * 8) = r;
+  }
+}
+
 // ---- SELayer -------------------------------------------------------------------------------
 // stage 1: block b of sample n sums a fixed pixel range for every channel (fixed order ->
 // deterministic); stage 2: one block per sample adds the partials in index order, divides by
@@ -268,6 +298,13 @@ extern "C" int vcm_maxpool2(const void* src, void* dst, int32_t N, int32_t H, in
                             int32_t src_cstride, int32_t dst_cstride, int32_t dtype, void* stream) {
   VCM_CHECK_ARG(src && dst && N > 0 && H > 1 && W > 1 && C > 0, "bad argument");
   const int64_t total = (int64_t)N * (H / 2) * (W / 2) * C;
+  if (dtype == VCM_BF16 && C % 8 == 0 && src_cstride % 8 == 0 && dst_cstride % 8 == 0 &&
+      (uintptr_t)src % 16 == 0 && (uintptr_t)dst % 16 == 0) {
+    maxpool2_bf16x8_kernel<<<ew_grid(total / 8), 256, 0, (cudaStream_t)stream>>>(
+        (const __nv_bfloat16*)src, (__nv_bfloat16*)dst, N, H, W, C, src_cstride, dst_cstride);
+    VCM_CHECK_LAUNCH();
+    return 0;
+  }
   VCM_DISPATCH_DTYPE(dtype, (maxpool2_kernel<T><<<ew_grid(total), 256, 0, (cudaStream_t)stream>>>(
                                 (const T*)src, (T*)dst, N, H, W, C, src_cstride, dst_cstride)));
   VCM_CHECK_LAUNCH();

@@ -178,6 +178,44 @@ __global__ void flow_warp_kernel(const T* __restrict__ feat, const float* __rest
   }
 }
 
+// bf16, 8 channels (16 bytes) per thread: same per-channel arithmetic, half the instructions and
+// twice the bytes in flight per thread of the 4-channel variant
+__global__ void flow_warp8_bf16_kernel(const __nv_bfloat16* __restrict__ feat, const float* __restrict__ flow,
+                                       __nv_bfloat16* __restrict__ out, int N, int H, int W, int C, int feat_cs,
+                                       int flow_cs, int out_cs) {
+  const int G = C / 8;
+  const int64_t total = (int64_t)N * H * W * G;
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total;
+       i += (int64_t)gridDim.x * blockDim.x) {
+    const int g = (int)(i % G);
+    const int64_t p = i / G;
+    const int ox = (int)(p % W);
+    const int64_t q = p / W;
+    const int oy = (int)(q % H);
+    const int n = (int)(q / H);
+    const float2 uv = __ldg(reinterpret_cast<const float2*>(flow + p * flow_cs));
+    const WarpTaps t = warp_taps(uv.x, uv.y, ox, oy, W, H);
+    const __nv_bfloat16* b = feat + (int64_t)n * H * W * feat_cs + g * 8;
+    const uint4 v00 = __ldg(reinterpret_cast<const uint4*>(b + ((int64_t)t.y0 * W + t.x0) * feat_cs));
+    const uint4 v01 = __ldg(reinterpret_cast<const uint4*>(b + ((int64_t)t.y0 * W + t.x1) * feat_cs));
+    const uint4 v10 = __ldg(reinterpret_cast<const uint4*>(b + ((int64_t)t.y1 * W + t.x0) * feat_cs));
+    const uint4 v11 = __ldg(reinterpret_cast<const uint4*>(b + ((int64_t)t.y1 * W + t.x1) * feat_cs));
+    const __nv_bfloat162* h00 = reinterpret_cast<const __nv_bfloat162*>(&v00);
+    const __nv_bfloat162* h01 = reinterpret_cast<const __nv_bfloat162*>(&v01);
+    const __nv_bfloat162* h10 = reinterpret_cast<const __nv_bfloat162*>(&v10);
+    const __nv_bfloat162* h11 = reinterpret_cast<const __nv_bfloat162*>(&v11);
+    uint4 r;
+    __nv_bfloat162* hr = reinterpret_cast<__nv_bfloat162*>(&r);
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const float2 a = __bfloat1622float2(h00[k]), bb = __bfloat1622float2(h01[k]);
+      const float2 cc = __bfloat1622float2(h10[k]), dd = __bfloat1622float2(h11[k]);
+      hr[k] = __floats2bfloat162_rn(warp_mix(t, a.x, bb.x, cc.x, dd.x), warp_mix(t, a.y, bb.y, cc.y, dd.y));
+    }
+    *reinterpret_cast<uint4*>(out + p * out_cs + g * 8) = r;
+  }
+}
+
 }  // namespace
 
 extern "C" int vcm_avgpool2(const float* src, float* dst, int32_t N, int32_t H, int32_t W, int32_t C,
@@ -219,6 +257,13 @@ extern "C" int vcm_flow_warp(const void* feat, const float* flow, void* out, int
                    ((uintptr_t)feat % (4 * esz) == 0) && ((uintptr_t)out % (4 * esz) == 0);
   const int64_t total = (int64_t)N * H * W * (vec ? C / 4 : C);
   cudaStream_t s = (cudaStream_t)stream;
+  if (dtype == VCM_BF16 && C % 8 == 0 && feat_cstride % 8 == 0 && out_cstride % 8 == 0 && flow_cstride % 2 == 0 &&
+      (uintptr_t)feat % 16 == 0 && (uintptr_t)out % 16 == 0 && (uintptr_t)flow % 8 == 0) {
+    flow_warp8_bf16_kernel<<<ew_grid((int64_t)N * H * W * (C / 8)), 256, 0, s>>>(
+        (const __nv_bfloat16*)feat, flow, (__nv_bfloat16*)out, N, H, W, C, feat_cstride, flow_cstride, out_cstride);
+    VCM_CHECK_LAUNCH();
+    return 0;
+  }
   VCM_DISPATCH_DTYPE(dtype, {
     if (vec)
       flow_warp_kernel<T, true><<<ew_grid(total), 256, 0, s>>>((const T*)feat, flow, (T*)out, N, H, W, C,

@@ -202,6 +202,27 @@ class CompressionModel(nn.Module):
             q = q.expand(N, -1)
         return q.to(rt.B.device, F32).contiguous()
 
+    # ---- NCHW fp32 tensors handed to callers keep their internal NHWC twin -------------------
+    @staticmethod
+    def _export(B, view, clamp=None):
+        """NHWC view -> the NCHW fp32 tensor callers see.  The view rides along (only when the values
+        are identical, i.e. no clamp) so that feeding the tensor back next frame skips the layout
+        round trip; an in-place edit by the caller bumps `_version` and invalidates it."""
+        t = B.to_nchw(view, clamp=clamp)
+        if clamp is None:
+            t._vcm_view = (view, t._version)
+        return t
+
+    @staticmethod
+    def _import(B, t, dtype=None):
+        """NCHW tensor from a caller -> NHWC view (cached twin if still valid)."""
+        hit = getattr(t, "_vcm_view", None)
+        want = dtype or B.act_dtype
+        if hit is not None and hit[1] == t._version and hit[0].dtype == want and \
+                hit[0].t.device == B.device and (hit[0].N, hit[0].C, hit[0].H, hit[0].W) == tuple(t.shape):
+            return hit[0]
+        return B.from_nchw(t, dtype=dtype)
+
     # ---- host <-> device symbol traffic -----------------------------------------------------
     @staticmethod
     def _to_host(*tensors):
@@ -264,7 +285,7 @@ class DMC(CompressionModel):
             xin, m = g.frame_input(dpb["ref_frame"])
             f = g.conv("feature_adaptor_I", xin, in_map=m)
         else:
-            f = g.conv("feature_adaptor_P", B.from_nchw(dpb["ref_feature"]))
+            f = g.conv("feature_adaptor_P", self._import(B, dpb["ref_feature"]))
         t, ta = g.conv_t("feature_extractor.conv1", f, 0.01)
         l1 = g.res_block("feature_extractor.res_block1", t, x_act=ta)
         t, ta = g.conv_t("feature_extractor.conv2", l1, 0.01, stride=2)
@@ -408,7 +429,7 @@ class DMC(CompressionModel):
 
     # ---- public API ------------------------------------------------------------------------------
     @torch.no_grad()
-    def compress(self, x, dpb, mv_y_q_scale, y_q_scale):
+    def compress(self, x, dpb, mv_y_q_scale, y_q_scale, _want_dpb=True):
         """video_model.py:263-352.  Stream order: z_mv, mv_y pass 0/1, z, y pass 0/1 (:333-340)."""
         rt = self._need_coder()
         assert x.shape[0] == 1, "the bitstream path is batch 1 (entropy_models.py:186)"
@@ -428,12 +449,14 @@ class DMC(CompressionModel):
         bit_stream = c.flush_encoder()
         self._last_symbols = dict(mv_z=mv_z, mv_y_q_w_0=ms0, mv_y_q_w_1=ms1, mv_idx_0=mi0, mv_idx_1=mi1,
                                   z=z, y_q_w_0=ys0, y_q_w_1=ys1, y_idx_0=yi0, y_idx_1=yi1)
+        if not _want_dpb:      # encode_decode() only uses the decoder's reconstruction
+            return {"dbp": None, "bit_stream": bit_stream}
         return {
             "dbp": {
-                "ref_frame": B.to_nchw(t["x_hat"]),
-                "ref_feature": B.to_nchw(t["feature"]),
-                "ref_y": B.to_nchw(t["y_hat"]),
-                "ref_mv_y": B.to_nchw(t["mv_y_hat"]),
+                "ref_frame": self._export(B, t["x_hat"]),
+                "ref_feature": self._export(B, t["feature"]),
+                "ref_y": self._export(B, t["y_hat"]),
+                "ref_mv_y": self._export(B, t["mv_y_hat"]),
             },
             "bit_stream": bit_stream,
         }
@@ -461,10 +484,10 @@ class DMC(CompressionModel):
         feature, x_hat = self._reconstruct(rt, y_hat, ctx, e2, e3)
         return {
             "dpb": {
-                "ref_frame": B.to_nchw(x_hat, clamp=(0.0, 1.0)),
-                "ref_feature": B.to_nchw(feature),
-                "ref_y": B.to_nchw(y_hat),
-                "ref_mv_y": B.to_nchw(mv_y_hat),
+                "ref_frame": self._export(B, x_hat, clamp=(0.0, 1.0)),
+                "ref_feature": self._export(B, feature),
+                "ref_y": self._export(B, y_hat),
+                "ref_mv_y": self._export(B, mv_y_hat),
             }
         }
 
@@ -473,7 +496,7 @@ class DMC(CompressionModel):
         mv_y_q_scale, mv_y_q_index = get_rounded_q(mv_y_q_scale)
         y_q_scale, y_q_index = get_rounded_q(y_q_scale)
         t0 = time.time()
-        encoded = self.compress(x, dpb, mv_y_q_scale, y_q_scale)
+        encoded = self.compress(x, dpb, mv_y_q_scale, y_q_scale, _want_dpb=False)
         blob = pack_p(encoded["bit_stream"], mv_y_q_index, y_q_index)
         t1 = time.time()
         a, b, string = unpack_p(blob)
@@ -489,7 +512,7 @@ class DMC(CompressionModel):
             mv_y_q_scale, mv_y_q_index = get_rounded_q(mv_y_q_scale)
             y_q_scale, y_q_index = get_rounded_q(y_q_scale)
             t0 = time.time()
-            encoded = self.compress(x, dpb, mv_y_q_scale, y_q_scale)
+            encoded = self.compress(x, dpb, mv_y_q_scale, y_q_scale, _want_dpb=False)
             encode_p(encoded["bit_stream"], mv_y_q_index, y_q_index, output_path)
             bits = filesize(output_path) * 8
             t1 = time.time()
