@@ -252,6 +252,35 @@ def test_se_layer(B32):
         assert torch.equal(got, got2), "SE reduction must be deterministic"
 
 
+def test_se_layer_bf16_vector_path(B16):
+    """bf16 activations take the vectorised partial-sum + striped reduction kernels."""
+    dev = "cuda:0"
+    g = torch.Generator().manual_seed(11)
+    for C, H, W in ((32, 128, 160), (64, 70, 90), (128, 33, 47)):
+        x = torch.randn((2, C, H, W), generator=g).to(dev).bfloat16()
+        w1 = (torch.randn((C // 16, C), generator=g) / C ** 0.5).to(dev).contiguous()
+        w2 = (torch.randn((C, C // 16), generator=g)).to(dev).contiguous()
+        want = torch.sigmoid(F.linear(F.relu(F.linear(x.float().mean(dim=(-1, -2)), w1)), w2))
+        xv = view_of(x.float(), dtype=torch.bfloat16, cs=C + 8, c0=8)
+        got = B16.se_scale(xv, w1, w2)
+        torch.testing.assert_close(got, want, rtol=1e-4, atol=1e-5)
+        assert torch.equal(got, B16.se_scale(xv, w1, w2)), "SE reduction must be deterministic"
+
+
+def test_bf16_warp_and_maxpool_vector_paths(B16):
+    from oracle import dcvc_oracle as O
+    dev = "cuda:0"
+    g = torch.Generator().manual_seed(12)
+    feat = torch.randn((2, 64, 40, 56), generator=g).to(dev).bfloat16()
+    flow = (torch.randn((2, 2, 40, 56), generator=g) * 4).to(dev)
+    fv = view_of(feat.float(), dtype=torch.bfloat16, cs=80, c0=16)
+    out = B16.warp(fv, view_of(flow))
+    want = O.torch_warp(feat.float().cpu(), flow.cpu()).to(dev)
+    torch.testing.assert_close(nchw(out), want.bfloat16().float(), rtol=2e-2, atol=2e-2)
+    mp = B16.maxpool(fv)
+    assert torch.equal(nchw(mp), F.max_pool2d(feat.float(), 2, 2))
+
+
 def test_motion_kernels(B32):
     from oracle import dcvc_oracle as O
     dev = "cuda:0"

@@ -136,6 +136,7 @@ __global__ void maxpool2_bf16x8_kernel(const __nv_bfloat16* __restrict__ src, __
 // deterministic); stage 2: one block per sample adds the partials in index order, divides by
 // H*W, and applies the two bias-free Linear layers.
 constexpr int SE_PIX_PER_BLOCK = 4096;
+constexpr int SE_PIX_PER_BLOCK_VEC = 1024;   // vectorised (bf16) path: 4x the blocks, fills the GPU at 1/4 resolution
 
 template <typename T>
 __global__ void se_partial_kernel(const T* __restrict__ x, float* __restrict__ partial, int64_t hw,
@@ -167,8 +168,8 @@ __global__ void __launch_bounds__(256) se_partial_vec_kernel(const T* __restrict
   const int n = blockIdx.y, b = blockIdx.x;
   const int c8 = C >> 3, rows = 256 / c8;
   const int u = threadIdx.x % c8, r = threadIdx.x / c8;
-  const int64_t p0 = (int64_t)b * SE_PIX_PER_BLOCK;
-  const int64_t p1 = (p0 + SE_PIX_PER_BLOCK < hw) ? p0 + SE_PIX_PER_BLOCK : hw;
+  const int64_t p0 = (int64_t)b * SE_PIX_PER_BLOCK_VEC;
+  const int64_t p1 = (p0 + SE_PIX_PER_BLOCK_VEC < hw) ? p0 + SE_PIX_PER_BLOCK_VEC : hw;
   float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
   if (r < rows) {
     const T* base = x + (int64_t)n * hw * cs + 8 * u;
@@ -227,6 +228,46 @@ __global__ void se_fc_kernel(const float* __restrict__ partial, const float* __r
     float s = 0.f;
     for (int j = 0; j < Cmid; ++j) s = fmaf(hid[j], w2[c * Cmid + j], s);
     scale[(int64_t)n * C + c] = 1.f / (1.f + expf(-s));
+  }
+}
+
+// Same, with the sum over the nblk partials striped over 256/C thread groups (fixed order: stripe
+// sums, then groups in index order) -- the serial loop above costs ~20 us at 1080p.
+__global__ void __launch_bounds__(256) se_fc_striped_kernel(const float* __restrict__ partial,
+                                                            const float* __restrict__ w1,
+                                                            const float* __restrict__ w2, float* __restrict__ scale,
+                                                            int64_t hw, int C, int Cmid, int nblk) {
+  extern __shared__ float sm[];  // part[groups][C] + mean[C] + hid[Cmid]
+  const int groups = 256 / C;
+  float* part = sm;
+  float* mean = sm + groups * C;
+  float* hid = mean + C;
+  const int n = blockIdx.x;
+  const int c = threadIdx.x % C, grp = threadIdx.x / C;
+  if (grp < groups) {
+    float s = 0.f;
+    const float* p = partial + (int64_t)n * nblk * C + c;
+#pragma unroll 8
+    for (int b = grp; b < nblk; b += groups) s += __ldg(p + (int64_t)b * C);
+    part[grp * C + c] = s;
+  }
+  __syncthreads();
+  if (threadIdx.x < C) {
+    float s = 0.f;
+    for (int k = 0; k < groups; ++k) s += part[k * C + threadIdx.x];
+    mean[threadIdx.x] = s / (float)hw;
+  }
+  __syncthreads();
+  for (int j = threadIdx.x; j < Cmid; j += blockDim.x) {
+    float s = 0.f;
+    for (int k = 0; k < C; ++k) s = fmaf(mean[k], w1[j * C + k], s);
+    hid[j] = fmaxf(s, 0.f);
+  }
+  __syncthreads();
+  for (int k = threadIdx.x; k < C; k += blockDim.x) {
+    float s = 0.f;
+    for (int j = 0; j < Cmid; ++j) s = fmaf(hid[j], w2[k * Cmid + j], s);
+    scale[(int64_t)n * C + k] = 1.f / (1.f + expf(-s));
   }
 }
 
@@ -311,7 +352,7 @@ extern "C" int vcm_maxpool2(const void* src, void* dst, int32_t N, int32_t H, in
   return 0;
 }
 
-extern "C" int32_t vcm_se_partial_count(int64_t hw) { return cdiv(hw, SE_PIX_PER_BLOCK); }
+extern "C" int32_t vcm_se_partial_count(int64_t hw) { return cdiv(hw, SE_PIX_PER_BLOCK_VEC); }   // upper bound of both paths
 
 extern "C" int vcm_se_scale(const void* x, float* partial, const float* w1, const float* w2,
                             float* scale, int32_t N, int64_t hw, int32_t C, int32_t Cmid,
@@ -326,12 +367,21 @@ extern "C" int vcm_se_scale(const void* x, float* partial, const float* w1, cons
   const bool vec = dtype == VCM_BF16 && C % 8 == 0 && cstride % 8 == 0 && ((uintptr_t)x & 15) == 0 && 256 % (C / 8) == 0;
   if (vec) {
     const int vrows = 256 / (C / 8);
-    VCM_DISPATCH_DTYPE(dtype, (se_partial_vec_kernel<T><<<dim3(nblk, N), 256, vrows * C * sizeof(float), s>>>(
-                                  (const T*)x, partial, hw, C, cstride, nblk)));
-  } else {
-    VCM_DISPATCH_DTYPE(dtype, (se_partial_kernel<T><<<dim3(nblk, N), threads, threads * sizeof(float), s>>>(
-                                  (const T*)x, partial, hw, C, cstride, nblk)));
+    const int vblk = cdiv(hw, SE_PIX_PER_BLOCK_VEC);
+    VCM_DISPATCH_DTYPE(dtype, (se_partial_vec_kernel<T><<<dim3(vblk, N), 256, vrows * C * sizeof(float), s>>>(
+                                  (const T*)x, partial, hw, C, cstride, vblk)));
+    VCM_CHECK_LAUNCH();
+    if (256 % C == 0) {
+      se_fc_striped_kernel<<<N, 256, ((256 / C) * C + C + Cmid) * sizeof(float), s>>>(partial, w1, w2, scale, hw, C,
+                                                                                     Cmid, vblk);
+    } else {
+      se_fc_kernel<<<N, 256, (C + Cmid) * sizeof(float), s>>>(partial, w1, w2, scale, hw, C, Cmid, vblk);
+    }
+    VCM_CHECK_LAUNCH();
+    return 0;
   }
+  VCM_DISPATCH_DTYPE(dtype, (se_partial_kernel<T><<<dim3(nblk, N), threads, threads * sizeof(float), s>>>(
+                                (const T*)x, partial, hw, C, cstride, nblk)));
   VCM_CHECK_LAUNCH();
   se_fc_kernel<<<N, 256, (C + Cmid) * sizeof(float), s>>>(partial, w1, w2, scale, hw, C, Cmid, nblk);
   VCM_CHECK_LAUNCH();
