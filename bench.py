@@ -209,7 +209,7 @@ def main():
     ap.add_argument("--precision", default=os.environ.get("VCM_B200_PRECISION", "bf16"))
     ap.add_argument("--impl", default="b200")
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--seqs-per-gpu", type=int, default=6,
+    ap.add_argument("--seqs-per-gpu", type=int, default=8,
                     help="independent sequences coded concurrently per GPU (own thread + CUDA stream each): "
                          "while one sequence's symbols are in the host rANS coder the other's convs run")
     a = ap.parse_args()

@@ -240,3 +240,48 @@ def test_batched_estimation_path(fp32_models):
                                 mv_y_q_scale=0.7, y_q_scale=0.7)
     torch.testing.assert_close(out["bpp"][1:], one["bpp"], rtol=1e-4, atol=1e-6)
     torch.testing.assert_close(out["dpb"]["ref_frame"][1:], one["dpb"]["ref_frame"], rtol=1e-4, atol=1e-5)
+
+
+def test_1080p_round_trip_properties(bf16_models):
+    """BASELINE size (1920x1080 padded to 1088), tensor-core mode, size-independent properties:
+    the stream decodes to exactly the encoder's reconstruction (latents, feature, frame), decoding
+    the stream again is idempotent, bits == 8 * container bytes, the coded symbols survive the host
+    coder (decode(encode(s)) == s for every plane), and a second identical call is bit-identical
+    (deterministic kernels)."""
+    from vcm_ts_b200.stream_helper import pack_p
+    dmc, intra = bf16_models
+    import bench as Bn
+    seq = Bn.synth_sequence(2, 3).cuda()
+    pad = lambda x: torch.nn.functional.pad(x, (0, Bn.WP - Bn.W, 0, Bn.HP - Bn.H))  # noqa: E731
+    r, blob_i = intra.encode_decode_bytes(pad(seq[0:1]), 1.0, Bn.H, Bn.W)
+    assert r["bit"] == 8 * len(blob_i)
+    dpb = {"ref_frame": r["x_hat"], "ref_feature": None, "ref_y": None, "ref_mv_y": None}
+    x = pad(seq[1:2])
+    enc = dmc.compress(x, dpb, 1.0, 1.0)
+    sym = {k: v.clone() for k, v in dmc._last_symbols.items()}
+    dec = dmc.decompress(dpb, enc["bit_stream"], Bn.H, Bn.W, 1.0, 1.0)
+    for k in ("ref_y", "ref_mv_y", "ref_feature"):
+        assert torch.equal(dec["dpb"][k], enc["dbp"][k]), k
+    assert torch.equal(dec["dpb"]["ref_frame"], enc["dbp"]["ref_frame"].clamp(0, 1))
+    dec2 = dmc.decompress(dpb, enc["bit_stream"], Bn.H, Bn.W, 1.0, 1.0)
+    for k in dec["dpb"]:
+        assert torch.equal(dec["dpb"][k], dec2["dpb"][k]), k
+    enc2 = dmc.compress(x, dpb, 1.0, 1.0)
+    assert enc2["bit_stream"] == enc["bit_stream"], "compress is not deterministic"
+    res, blob = dmc.encode_decode_bytes(x, dpb, Bn.H, Bn.W, 1.0, 1.0)
+    assert res["bit"] == 8 * len(blob) and blob == pack_p(enc["bit_stream"], 100, 100)
+    # symbols through the host coder
+    rt = dmc._rt
+    rt.coder.set_stream(enc["bit_stream"])
+    out = torch.empty(sym["mv_z"].shape, dtype=torch.int16)
+    rt.coder.decode_channels(64, out.shape[2] * out.shape[3], rt.tables["bit_estimator_z_mv"], out)
+    assert torch.equal(out, sym["mv_z"])
+    for s, i in (("mv_y_q_w_0", "mv_idx_0"), ("mv_y_q_w_1", "mv_idx_1")):
+        o = torch.empty(sym[s].shape, dtype=torch.int16)
+        rt.coder.decode_planes(sym[i], rt.tables["y"], o)
+        assert torch.equal(o, sym[s]), s
+    n_sym = sum(sym[k].numel() for k in ("mv_z", "z", "mv_y_q_w_0", "mv_y_q_w_1", "y_q_w_0", "y_q_w_1"))
+    assert n_sym == 1370880          # SURVEY 8(d): symbols per 1080p P-frame
+    psnr = _psnr(x[..., :Bn.H, :Bn.W].cpu(), res["dpb"]["ref_frame"][..., :Bn.H, :Bn.W].cpu())
+    assert math.isfinite(psnr) and psnr > 3.0, psnr   # random-init weights: only a sanity bound
+    assert float(res["dpb"]["ref_frame"].min()) >= 0.0 and float(res["dpb"]["ref_frame"].max()) <= 1.0
