@@ -6,8 +6,10 @@
 One "step" = one synthetic GOP of `--gop` frames (1 I-frame through IntraNoAR + P-frames through
 DMC), 1920x1080 padded to 1920x1088, each frame going through the public
 `encode_decode`-equivalent call (compress -> real rANS bitstream -> decompress).  Every rank codes
-its own independent sequence (the path shards by sequence / GOP with no data-path collective), so
-scaling is "weak".  Two timed passes:
+its own independent sequences (the path shards by sequence / GOP with no data-path collective), so
+scaling is "weak".  `--seqs-per-gpu S` (default 8, BASELINE config 4) sequences are coded concurrently
+per GPU, one Python thread + CUDA stream each, so the sequential host rANS coder of one sequence
+overlaps the convolutions of the others; `single_sequence_frames_per_s` is the S=1 latency view.  Two timed passes:
 
   value : frames already resident in HBM, reconstruction left in HBM;
   e2e   : frames start in pinned host memory (H2D inside the timed region) and every reconstructed
