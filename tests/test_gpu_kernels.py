@@ -217,6 +217,32 @@ def test_conv_tcgen05_engine(B16, case):
         assert bool(((nchw(out2) - w2).abs() <= 0.01 * w2.abs() + 0.02).all())
 
 
+def test_conv_tcgen05_unaligned_views_take_scalar_epilogue(B16):
+    """Output / residual views whose channel stride or offset is not a multiple of 8 cannot use the
+    16-byte vector epilogue: the tensor-core engine must still take the conv (scalar bf16 epilogue)."""
+    import ctypes
+    from vcm_ts_b200 import _lib
+    from vcm_ts_b200.backend import View
+    g = torch.Generator(device="cpu").manual_seed(77)
+    dev, bf = "cuda:0", torch.bfloat16
+    N, Cin, Cout, H, W = 1, 64, 64, 21, 35
+    x = torch.randn((N, Cin, H, W), generator=g).to(dev).to(bf)
+    w = (torch.randn((Cout, Cin, 3, 3), generator=g) / 24).to(dev)
+    b = torch.randn((Cout,), generator=g).to(dev)
+    res = torch.randn((N, Cout, H, W), generator=g).to(dev).to(bf)
+    pc = B16.pack_conv(w, b)
+    out_buf = View(torch.zeros((N, H, W, Cout + 6), dtype=bf, device=dev), 3, Cout)   # cs = 70, c0 = 3
+    rv = view_of(res.float(), dtype=bf, cs=Cout + 4, c0=4)
+    d = _lib.ConvDesc(N, H, W, Cin, Cout, 3, 1, Cin, out_buf.cs, rv.cs, 0, 0, _lib.CONV_RES | _lib.CONV_POST_ACT,
+                      0.0, 0.1, 0.0, _lib.BF16, _lib.BF16)
+    assert B16.L.vcm_conv2d_tc_supported(ctypes.byref(d)) == 1
+    out = B16.conv(view_of(x.float(), dtype=bf), pc, out=out_buf, post=0.1, res=rv)
+    want = ref_conv(x.float(), w.to(bf).float(), b, 1, None, 0.1, False, res.float(), None, None)
+    got = nchw(out)
+    assert bool(((got - want).abs() <= 0.01 * want.abs() + 0.02).all()), (got - want).abs().max().item()
+    assert float(out_buf.t[..., :3].abs().max()) == 0.0 and float(out_buf.t[..., 3 + Cout:].abs().max()) == 0.0
+
+
 def test_layout_and_pool_kernels(B32):
     dev = "cuda:0"
     g = torch.Generator().manual_seed(0)

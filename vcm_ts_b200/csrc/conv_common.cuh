@@ -25,7 +25,6 @@ struct ConvParams {
   int flags;
   float pre_slope, post_slope, out2_slope;
   int cin_chunks, vecA, vecB, tiles_x, tiles_y;
-  int debug;   // VCM_TC_DEBUG bit mask (profiling experiments only; 0 in normal use)
 };
 
 template <typename T>
@@ -70,9 +69,5 @@ static inline int conv_fill_params(const vcm_conv_desc* d, ConvParams& P) {
   P.res_cs = d->res_cstride; P.res2_cs = d->res2_cstride; P.out2_cs = d->out2_cstride;
   P.flags = d->flags; P.pre_slope = d->pre_slope; P.post_slope = d->post_slope;
   P.out2_slope = d->out2_slope;
-  {
-    static const int dbg = getenv("VCM_TC_DEBUG") ? atoi(getenv("VCM_TC_DEBUG")) : 0;
-    P.debug = dbg;
-  }
   return 0;
 }

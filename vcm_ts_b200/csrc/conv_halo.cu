@@ -58,7 +58,7 @@ struct HaloBars {
 // single-thread region.  The other lanes only take part in the barrier waits.
 template <int CHUNK, int K, int MH, bool RESIDENT>
 __device__ __forceinline__ void mma_role(const HaloGeom& G, const HaloBars& B, uint32_t a_smem, uint32_t b_smem,
-                                         uint32_t tmem_base, int dbg) {
+                                         uint32_t tmem_base) {
   constexpr uint32_t LAYOUT = CHUNK == 64 ? 2u : (CHUNK == 32 ? 4u : 6u);
   constexpr uint32_t ROWB = CHUNK * 2u;
   constexpr int KSTEPS = CHUNK / 16;
@@ -103,9 +103,8 @@ __device__ __forceinline__ void mma_role(const HaloGeom& G, const HaloBars& B, u
             const uint64_t adesc = adesc0 + (uint64_t)(ky * ALINE16 + kx * AROW16);
 #pragma unroll
             for (int k = 0; k < KSTEPS; ++k)
-              if (!(dbg & 4) || (tap == 0 && k == 0))
-                umma_bf16(d_tmem, adesc + (uint64_t)(2 * k), bdesc + (uint64_t)(2 * k), idesc,
-                          (tap > 0 || k > 0) ? 1u : (ch > 0 ? 1u : 0u));
+              umma_bf16(d_tmem, adesc + (uint64_t)(2 * k), bdesc + (uint64_t)(2 * k), idesc,
+                        (tap > 0 || k > 0) ? 1u : (ch > 0 ? 1u : 0u));
             if (MH == 2) {
 #pragma unroll
               for (int k = 0; k < KSTEPS; ++k)
@@ -221,9 +220,9 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     const uint32_t a_smem = smem_u32(smem), b_smem = smem_u32(smem + G.b_base);
 #define HALO_MMA(KK)                                                                              \
   do {                                                                                            \
-    if (G.resident) mma_role<CHUNK, KK, 1, true>(G, B, a_smem, b_smem, tmem_base, P.debug);                 \
-    else if (G.mh == 1) mma_role<CHUNK, KK, 1, false>(G, B, a_smem, b_smem, tmem_base, P.debug);            \
-    else mma_role<CHUNK, KK, 2, false>(G, B, a_smem, b_smem, tmem_base, P.debug);                           \
+    if (G.resident) mma_role<CHUNK, KK, 1, true>(G, B, a_smem, b_smem, tmem_base);                 \
+    else if (G.mh == 1) mma_role<CHUNK, KK, 1, false>(G, B, a_smem, b_smem, tmem_base);            \
+    else mma_role<CHUNK, KK, 2, false>(G, B, a_smem, b_smem, tmem_base);                           \
   } while (0)
     if (P.K == 3) HALO_MMA(3);
     else if (P.K == 1) HALO_MMA(1);
