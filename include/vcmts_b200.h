@@ -99,6 +99,14 @@ int vcm_tma_probe(const void* img, int32_t H, int32_t W, int32_t bw, int32_t bh,
 /* NCHW fp32 -> NHWC view (dtype) ; callers' tensors are NCHW fp32 (video_coder.py:99-117)  */
 int vcm_nchw_to_nhwc(const float* src, void* dst, int32_t N, int32_t C, int32_t H, int32_t W,
                      int32_t dst_cstride, int32_t dtype, void* stream);
+/* frame I/O: uint8 HWC [N][H][W][3] (PNG decode output, DCVC_HEM/src/utils/png_reader.py:37-39) ->
+ * float NCHW [N][3][Hp][Wp] = u8 / 255.f, zero-padded right / bottom (test_video.py:118-125,
+ * video_coder.py:112); and the inverse of save_torch_image (stream_helper.py:151-154):
+ * crop to H x W, clip(rint(v * 255), 0, 255) from a float NCHW [N][3][Hs][Ws] reconstruction.        */
+int vcm_u8hwc_to_frame(const uint8_t* src, float* dst, int32_t N, int32_t H, int32_t W, int32_t Hp,
+                       int32_t Wp, void* stream);
+int vcm_frame_to_u8hwc(const float* src, uint8_t* dst, int32_t N, int32_t H, int32_t W, int32_t Hs,
+                       int32_t Ws, void* stream);
 /* NHWC view -> NCHW fp32, optional clamp to [lo,hi] (video_model.py:413 `recon.clamp(0,1)`)  */
 int vcm_nhwc_to_nchw(const void* src, float* dst, int32_t N, int32_t C, int32_t H, int32_t W,
                      int32_t src_cstride, int32_t dtype, int32_t do_clamp, float lo, float hi,

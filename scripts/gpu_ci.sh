@@ -11,7 +11,7 @@ run() { # name timeout cmd...
 }
 STAGES=${STAGES:-"k_fp32 k_tc e2e_fp32 e2e_bf16 smoke bench"}
 for s in $STAGES; do case $s in
-  k_fp32) run k_fp32 150 python -m pytest tests/test_gpu_kernels.py -m gpu -q -k "fp32_engine or mixed or layout or se_layer or motion or dual_prior or round_and_bits or vector_path" ;;
+  k_fp32) run k_fp32 150 python -m pytest tests/test_gpu_kernels.py -m gpu -q -k "fp32_engine or mixed or layout or se_layer or motion or dual_prior or round_and_bits or vector_path or frame_io" ;;
   k_probe) run k_probe 100 python -m pytest tests/test_gpu_kernels.py -m gpu -q -s -k "probe" ;;
   k_tc) run k_tc 150 python -m pytest tests/test_gpu_kernels.py -m gpu -q -k "tcgen05" ;;
   e2e_fp32) run e2e_fp32 300 python -m pytest tests/test_gpu_e2e.py -m gpu -q -s -k "fp32 or batched" ;;

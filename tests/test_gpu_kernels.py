@@ -472,3 +472,31 @@ def test_conv_tcgen05_padded_and_fp32_out(B16, case):
     want = ref_conv(x.float(), w.to(bf).float(), b, 1, None, None, ps, res, None, None)
     got = nchw(out)
     assert bool(((got - want).abs() <= 0.01 * want.abs() + 0.02).all()), (got - want).abs().max().item()
+
+
+def test_frame_io_bit_exact_vs_reference_formulas():
+    """uint8 HWC <-> float NCHW on the device against the reference's numpy formulas
+    (png_reader.py:37-39 `asarray(...).astype('float32').transpose(2,0,1) / 255.`, zero pad;
+    stream_helper.py:151-154 `clip(rint(img * 255), 0, 255).astype(uint8)`): bit-exact, incl. ragged
+    sizes, half-way values and out-of-range reconstructions."""
+    from vcm_ts_b200 import frame_io
+    rng = np.random.default_rng(5)
+    for N, H, W in ((1, 240, 416), (2, 37, 53), (1, 1080, 1920)):
+        u8 = rng.integers(0, 256, size=(N, H, W, 3), dtype=np.uint8)
+        got = frame_io.frames_from_u8(torch.from_numpy(u8).pin_memory(), device="cuda:0")
+        want = u8.astype("float32").transpose(0, 3, 1, 2) / 255.
+        Hp, Wp = (H + 63) // 64 * 64, (W + 63) // 64 * 64
+        assert tuple(got.shape) == (N, 3, Hp, Wp)
+        assert np.array_equal(got[:, :, :H, :W].cpu().numpy(), want)
+        assert float(got[:, :, H:, :].abs().sum()) == 0.0 and float(got[:, :, :, W:].abs().sum()) == 0.0
+        # way back: exact round trip for in-range frames
+        back = frame_io.frames_to_u8(got, H, W)
+        assert np.array_equal(back.cpu().numpy(), u8)
+        # arbitrary floats incl. x.5 / 255 ties, negatives and > 1
+        f = rng.normal(0.5, 0.6, size=(N, 3, Hp, Wp)).astype("float32")
+        f[0, 0, 0, :8] = (np.arange(8, dtype="float32") + 0.5) / 255.0
+        want_u8 = np.clip(np.rint(f.transpose(0, 2, 3, 1)[:, :H, :W] * 255), 0, 255).astype(np.uint8)
+        host = torch.empty((N, H, W, 3), dtype=torch.uint8).pin_memory()
+        frame_io.frames_to_u8(torch.from_numpy(f).cuda(), H, W, out=host)
+        torch.cuda.synchronize()
+        assert np.array_equal(host.numpy(), want_u8)

@@ -49,6 +49,8 @@ _PROTOS = {
     "vcm_umma_rate2": (c_int, [c_int32, c_int32, c_int32, c_int32, _P, _P]),
     "vcm_tma_probe": (c_int, [_P, c_int32, c_int32, c_int32, c_int32, c_int32, c_int32, _P, _P]),
     "vcm_nchw_to_nhwc": (c_int, [_P, _P, c_int32, c_int32, c_int32, c_int32, c_int32, c_int32, _P]),
+    "vcm_u8hwc_to_frame": (c_int, [_P, _P, c_int32, c_int32, c_int32, c_int32, c_int32, _P]),
+    "vcm_frame_to_u8hwc": (c_int, [_P, _P, c_int32, c_int32, c_int32, c_int32, c_int32, _P]),
     "vcm_nhwc_to_nchw": (c_int, [_P, _P, c_int32, c_int32, c_int32, c_int32, c_int32, c_int32,
                                  c_int32, c_float, c_float, _P]),
     "vcm_copy_channels": (c_int, [_P, _P, c_int64, c_int32, c_int32, c_int32, c_int32, c_int32, _P]),

@@ -271,6 +271,43 @@ __global__ void __launch_bounds__(256) se_fc_striped_kernel(const float* __restr
   }
 }
 
+// ---- frame I/O ---------------------------------------------------------
+// uint8 HWC frame (what PNG decoding yields, png_reader.py:37-39) -> float NCHW `u8 / 255.f`, zero-padded
+// right / bottom to (Hp, Wp) (test_video.py:118-125, video_coder.py:112); and the way back,
+// save_torch_image (stream_helper.py:151-154): crop, clip(rint(v * 255), 0, 255).
+__global__ void u8hwc_to_frame_kernel(const uint8_t* __restrict__ src, float* __restrict__ dst, int N, int H,
+                                      int W, int Hp, int Wp) {
+  const int64_t total = (int64_t)N * 3 * Hp * Wp;
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total;
+       i += (int64_t)gridDim.x * blockDim.x) {
+    const int x = (int)(i % Wp);
+    int64_t r = i / Wp;
+    const int y = (int)(r % Hp);
+    r /= Hp;
+    const int c = (int)(r % 3);
+    const int n = (int)(r / 3);
+    float v = 0.f;
+    if (y < H && x < W) v = __fdiv_rn((float)src[(((int64_t)n * H + y) * W + x) * 3 + c], 255.f);
+    dst[i] = v;
+  }
+}
+
+__global__ void frame_to_u8hwc_kernel(const float* __restrict__ src, uint8_t* __restrict__ dst, int N, int H,
+                                      int W, int Hs, int Ws) {
+  const int64_t total = (int64_t)N * H * W * 3;
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total;
+       i += (int64_t)gridDim.x * blockDim.x) {
+    const int c = (int)(i % 3);
+    int64_t r = i / 3;
+    const int x = (int)(r % W);
+    r /= W;
+    const int y = (int)(r % H);
+    const int n = (int)(r / H);
+    const float v = rintf(__fmul_rn(src[(((int64_t)n * 3 + c) * Hs + y) * Ws + x], 255.f));
+    dst[i] = (uint8_t)fminf(fmaxf(v, 0.f), 255.f);
+  }
+}
+
 inline int ew_grid(int64_t total) {
   int64_t g = (total + 255) / 256;
   return (int)(g > 148 * 16 ? 148 * 16 : (g < 1 ? 1 : g));
@@ -285,6 +322,22 @@ extern "C" int vcm_nchw_to_nhwc(const float* src, void* dst, int32_t N, int32_t 
   dim3 grid(cdiv(HW, 32), cdiv(C, 32), N), block(32, 8);
   VCM_DISPATCH_DTYPE(dtype, (nchw_to_nhwc_kernel<T><<<grid, block, 0, (cudaStream_t)stream>>>(
                                 src, (T*)dst, C, HW, dst_cstride)));
+  VCM_CHECK_LAUNCH();
+  return 0;
+}
+
+extern "C" int vcm_u8hwc_to_frame(const uint8_t* src, float* dst, int32_t N, int32_t H, int32_t W, int32_t Hp,
+                                  int32_t Wp, void* stream) {
+  VCM_CHECK_ARG(src && dst && N > 0 && H > 0 && W > 0 && Hp >= H && Wp >= W, "bad argument");
+  u8hwc_to_frame_kernel<<<ew_grid((int64_t)N * 3 * Hp * Wp), 256, 0, (cudaStream_t)stream>>>(src, dst, N, H, W, Hp, Wp);
+  VCM_CHECK_LAUNCH();
+  return 0;
+}
+
+extern "C" int vcm_frame_to_u8hwc(const float* src, uint8_t* dst, int32_t N, int32_t H, int32_t W, int32_t Hs,
+                                  int32_t Ws, void* stream) {
+  VCM_CHECK_ARG(src && dst && N > 0 && H > 0 && W > 0 && Hs >= H && Ws >= W, "bad argument");
+  frame_to_u8hwc_kernel<<<ew_grid((int64_t)N * H * W * 3), 256, 0, (cudaStream_t)stream>>>(src, dst, N, H, W, Hs, Ws);
   VCM_CHECK_LAUNCH();
   return 0;
 }
