@@ -12,8 +12,9 @@ per GPU, one Python thread + CUDA stream each, so the sequential host rANS coder
 overlaps the convolutions of the others; `single_sequence_frames_per_s` is the S=1 latency view.  Two timed passes:
 
   value : frames already resident in HBM, reconstruction left in HBM;
-  e2e   : frames start in pinned host memory (H2D inside the timed region) and every reconstructed
-          frame is copied back to pinned host memory (D2H inside the timed region).
+  e2e   : frames start as uint8 HWC in pinned host memory (what a PNG decoder yields; H2D, /255 and
+          padding inside the timed region) and every reconstructed frame is converted back to uint8 HWC
+          and copied to pinned host memory (D2H inside the timed region).
 
 Both passes include the D2H of symbols/indexes, the CPU rANS coder and the H2D of decoded symbols:
 that hand-off is part of the path (the bitstream is produced and consumed on the host).
@@ -114,16 +115,18 @@ class ClockSampler:
 
 
 def code_gop(dmc, intra, frames_src, gop, q, host_out=None, pinned_in=False, dev=None):
-    """Encode+decode one GOP.  frames_src[t]: [3,1080,1920] (device, or pinned host when pinned_in).
-    Returns (bits, last reconstruction)."""
-    F = torch.nn.functional
+    """Encode+decode one GOP.  frames_src[t]: padded float [3,1088,1920] on the device, or (pinned_in)
+    a pinned-host uint8 [1080,1920,3] frame -- what a PNG decoder hands over -- that is copied to
+    the device, normalised and padded there (vcm_ts_b200.frame_io).  host_out: pinned uint8
+    [gop,1080,1920,3] that receives every reconstruction.  Returns (bits, last reconstruction)."""
+    from vcm_ts_b200 import frame_io
     bits = 0
     dpb = None
     for t in range(gop):
-        fr = frames_src[t]
         if pinned_in:
-            fr = fr.to(dev, non_blocking=True)
-        x = F.pad(fr[None], (0, WP - W, 0, HP - H))
+            x = frame_io.frames_from_u8(frames_src[t], device=dev)
+        else:
+            x = frames_src[t][None]
         if t == 0:
             r, _ = intra.encode_decode_bytes(x, q, H, W)
             rec = r["x_hat"]
@@ -134,7 +137,7 @@ def code_gop(dmc, intra, frames_src, gop, q, host_out=None, pinned_in=False, dev
             rec = dpb["ref_frame"]
         bits += r["bit"]
         if host_out is not None:
-            host_out[t].copy_(rec[0, :, :H, :W], non_blocking=True)
+            frame_io.frames_to_u8(rec, H, W, out=host_out[t:t + 1])
     return bits, rec
 
 
@@ -271,9 +274,14 @@ def main():
         dmc_k, intra_k = dmc_k.to(dev), intra_k.to(dev)
         dmc_k.update(force=True)
         intra_k.update(force=True)
-        sh = synth_sequence(gop, my_units[k]).pin_memory()
-        workers.append(dict(dmc=dmc_k, intra=intra_k, seq_host=sh, seq_dev=sh.to(dev),
-                            host_out=torch.empty((gop, 3, H, W), dtype=torch.float32).pin_memory(),
+        # 8-bit frames, as video is: uint8 HWC in pinned host memory for the e2e arm, and the same
+        # frames normalised + padded on the device for the resident arm
+        from vcm_ts_b200 import frame_io
+        sh = (synth_sequence(gop, my_units[k]) * 255.0).round().to(torch.uint8).permute(0, 2, 3, 1).contiguous()
+        sh = sh.pin_memory()
+        sd = torch.cat([frame_io.frames_from_u8(sh[t0:t0 + 4], device=dev) for t0 in range(0, gop, 4)])
+        workers.append(dict(dmc=dmc_k, intra=intra_k, seq_host=sh, seq_dev=sd,
+                            host_out=torch.empty((gop, H, W, 3), dtype=torch.uint8).pin_memory(),
                             stream=torch.cuda.Stream(dev), bits=0))
     dmc, intra, seq_dev = workers[0]["dmc"], workers[0]["intra"], workers[0]["seq_dev"]
 
@@ -363,8 +371,7 @@ def main():
     cpu = None
     if rank == 0:
         F = torch.nn.functional
-        x1 = F.pad(seq_dev[1:2], (0, WP - W, 0, HP - H))
-        x0 = F.pad(seq_dev[0:1], (0, WP - W, 0, HP - H))
+        x1, x0 = seq_dev[1:2], seq_dev[0:1]
         r0, _ = intra.encode_decode_bytes(x0, q, H, W)
         dpb = {"ref_frame": r0["x_hat"], "ref_feature": None, "ref_y": None, "ref_mv_y": None}
         rf = conv_roofline(dmc, intra, x1, dpb, q)
@@ -395,7 +402,7 @@ def main():
             cpu = {"value": gop / per_gop, "unit": "frames/s", "cores": threads, "kind": "port",
                    "sample": ob["sample"]}
     if rank == 0:
-        seq_bytes = S * gop * 3 * H * W * 4
+        seq_bytes = S * gop * 3 * H * W      # uint8 frames in, uint8 reconstructions out
         print(json.dumps({
             "metric": METRIC, "value": value, "unit": "frames/s", "n_gpus": world, "steps": a.steps,
             "warmup": a.warmup, "ms_per_step": ms_res / a.steps, "higher_is_better": True, "scaling": "weak",
