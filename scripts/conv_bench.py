@@ -30,6 +30,9 @@ SHAPES = {
     "k7_16_2_full": (7, 1, 16, 2, 1088, 1920, False, False),
     "k1_64_64_full": (1, 1, 64, 64, 1088, 1920, True, False),
     "c64_256ps_q": (3, 1, 64, 256, 272, 480, False, True),
+    "c192_192_16": (3, 1, 192, 192, 68, 120, False, False),
+    "c64_64_8": (3, 1, 64, 64, 136, 240, True, False),
+    "c128_128_q2": (3, 1, 128, 128, 272, 480, False, False),
     "c384_288_16": (3, 1, 384, 288, 68, 120, False, False),
 }
 

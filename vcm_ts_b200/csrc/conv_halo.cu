@@ -289,6 +289,17 @@ int vcm_conv_halo_launch(const vcm_conv_desc* d, const ConvParams& P, const void
   memset(&G, 0, sizeof(G));
   const int chunk = pick_chunk(P.Cin);
   pick_n_tiling(P.Cout, G.cout_p, G.bn, G.n_tiles);
+  // Small images (the 1/16-scale prior / hyper nets: 75 spatial tiles at 1080p) cannot fill 148 SMs with
+  // one N tile: cut Cout into more, narrower N tiles (the activation tile is re-read from L2 instead).
+  const int sp1 = cdiv(P.Wo, HTW) * cdiv(P.Ho, HTH) * P.N;
+  if (sp1 * G.n_tiles < num_sms()) {
+    for (int nt = G.n_tiles + 1; nt <= G.cout_p / 32; ++nt) {
+      if (G.cout_p % nt || (G.cout_p / nt) % 16) continue;
+      G.n_tiles = nt;
+      G.bn = G.cout_p / nt;
+      if (sp1 * nt >= num_sms()) break;
+    }
+  }
   G.nchunks = P.Cin / chunk;
   G.ntaps = P.K * P.K;
   G.hw = HTW + P.K - 1;
@@ -308,7 +319,8 @@ int vcm_conv_halo_launch(const vcm_conv_desc* d, const ConvParams& P, const void
     G.a_stage_bytes = a_stage(1);
     G.a_stages = (budget - slabs * G.b_slot_bytes) / G.a_stage_bytes;
   } else {
-    G.mh = (G.bn <= 128 && P.Ho > HTH) ? 2 : 1;
+    // 256-pixel items halve the weight traffic per pixel, but only when they still give every SM an item
+    G.mh = (G.bn <= 128 && P.Ho > HTH && cdiv(P.Wo, HTW) * cdiv(P.Ho, 2 * HTH) * P.N * G.n_tiles >= num_sms()) ? 2 : 1;
     G.a_stage_bytes = a_stage(G.mh);
     G.a_stages = 3;
     if (G.a_stages * G.a_stage_bytes > budget / 2) G.a_stages = 2;
