@@ -357,15 +357,27 @@ def main():
     value = frames_total / (ms_res * 1e-3)
     e2e = frames_total / (ms_e2e * 1e-3)
     bpp = workers[0]["bits"] / float(gop * H * W)
-    single = None
+    single = single_pipe = None
     if S > 1 and rank == 0:
-        # latency view: ONE sequence alone on the GPU (GPU idles while its symbols are in the host coder)
-        n1 = min(gop, 8)
+        # ONE sequence alone on the GPU (BASELINE config 2).  serial: frame-by-frame encode_decode, the GPU
+        # idles while the frame's symbols are in the host coder; pipelined: vcm_ts_b200.pipeline.GopPipeline
+        # overlaps encoder / host coder / decoder across the frames of the GOP (same bytes, same frames).
+        from vcm_ts_b200.pipeline import GopPipeline
+        n1 = min(gop, 16)
         torch.cuda.synchronize()
         t0 = time.time()
         code_gop(dmc, intra, seq_dev, n1, q)
         torch.cuda.synchronize()
         single = n1 / (time.time() - t0)
+        w0, w1 = workers[0], workers[1]
+        pipe = GopPipeline((w1["dmc"], w1["intra"]), (w0["dmc"], w0["intra"]), dev)
+        frames = [w0["seq_dev"][t:t + 1] for t in range(n1)]
+        pipe.code_gop(frames[:3], H, W, q, q, q)
+        torch.cuda.synchronize()
+        t0 = time.time()
+        pipe.code_gop(frames, H, W, q, q, q)
+        torch.cuda.synchronize()
+        single_pipe = n1 / (time.time() - t0)
 
     roof = None
     cpu = None
@@ -407,7 +419,7 @@ def main():
             "metric": METRIC, "value": value, "unit": "frames/s", "n_gpus": world, "steps": a.steps,
             "warmup": a.warmup, "ms_per_step": ms_res / a.steps, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "bf16" if a.precision == "bf16" else "f32", "data": "synthetic",
-            "config": cfg, "clocks": clk, "bpp": bpp, "single_sequence_frames_per_s": single,
+            "config": cfg, "clocks": clk, "bpp": bpp, "single_sequence_frames_per_s": {"serial": single, "pipelined": single_pipe},
             "e2e": {"value": e2e, "unit": "frames/s", "h2d_bytes_per_step": seq_bytes,
                     "d2h_bytes_per_step": seq_bytes, "ms_per_step": ms_e2e / a.steps},
             "gpu_launches": launches, "roofline": roof, "cpu_baseline": cpu}))

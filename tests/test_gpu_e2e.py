@@ -285,3 +285,37 @@ def test_1080p_round_trip_properties(bf16_models):
     psnr = _psnr(x[..., :Bn.H, :Bn.W].cpu(), res["dpb"]["ref_frame"][..., :Bn.H, :Bn.W].cpu())
     assert math.isfinite(psnr) and psnr > 3.0, psnr   # random-init weights: only a sanity bound
     assert float(res["dpb"]["ref_frame"].min()) >= 0.0 and float(res["dpb"]["ref_frame"].max()) <= 1.0
+
+
+@pytest.mark.parametrize("precision", ["bf16", "fp32"])
+def test_gop_pipeline_equals_serial_coding(precision):
+    """pipeline.GopPipeline (encoder / host coder / decoder overlapped across frames) must produce
+    byte-identical containers and bit-identical decoder reconstructions to frame-by-frame
+    encode_decode: the encoder predicting from its own reconstruction changes nothing."""
+    from oracle import fixture
+    from vcm_ts_b200.pipeline import GopPipeline
+    dev = "cuda:0"
+    enc, dec = _models(precision), _models(precision)
+    fr = fixture.fixture_frames(128, 192, 5, seed=9).to(dev)
+    # serial reference through the public per-frame calls
+    dmc, intra = dec
+    want_blobs, want_rec = [], []
+    r, blob = intra.encode_decode_bytes(fr[0:1], 1.0, 128, 192)
+    want_blobs.append(blob)
+    want_rec.append(r["x_hat"].clone())
+    dpb = {"ref_frame": r["x_hat"], "ref_feature": None, "ref_y": None, "ref_mv_y": None}
+    for t in range(1, 5):
+        r, blob = dmc.encode_decode_bytes(fr[t:t + 1], dpb, 128, 192, 1.0, 1.0)
+        dpb = r["dpb"]
+        want_blobs.append(blob)
+        want_rec.append(dpb["ref_frame"].clone())
+    got_rec = {}
+    pipe = GopPipeline(enc, dec, dev)
+    for _ in range(2):       # twice: the pipeline object is reusable
+        got_rec.clear()
+        blobs = pipe.code_gop([fr[t:t + 1] for t in range(5)], 128, 192, 1.0, 1.0, 1.0,
+                              on_recon=lambda t, x: got_rec.__setitem__(t, x.clone()))
+        torch.cuda.synchronize()
+        assert blobs == want_blobs
+        for t in range(5):
+            assert torch.equal(got_rec[t], want_rec[t]), t

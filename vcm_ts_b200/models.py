@@ -429,14 +429,31 @@ class DMC(CompressionModel):
 
     # ---- public API ------------------------------------------------------------------------------
     @torch.no_grad()
-    def compress(self, x, dpb, mv_y_q_scale, y_q_scale, _want_dpb=True):
-        """video_model.py:263-352.  Stream order: z_mv, mv_y pass 0/1, z, y pass 0/1 (:333-340)."""
+    def compress_symbols(self, x, dpb, mv_y_q_scale, y_q_scale, want_dpb=True, clamp_ref=False):
+        """Device half of compress(): analysis nets + quantisation, symbols / scale indexes copied to
+        the host.  Returns (host symbol tuple in stream order, dpb or None).  clamp_ref: ref_frame
+        clamped to [0,1] like the decoder's (video_model.py:413), for encoder-side prediction chains
+        (pipeline.py)."""
         rt = self._need_coder()
         assert x.shape[0] == 1, "the bitstream path is batch 1 (entropy_models.py:186)"
         B = rt.B
         t = self._analyse(x, dpb, mv_y_q_scale, y_q_scale, want_full=False)
-        host = self._to_host(t["mv_z_sym"], *t["mv_dp"]["sym"], *t["mv_dp"]["idx"],
-                             t["z_sym"], *t["y_dp"]["sym"], *t["y_dp"]["idx"])
+        host = tuple(self._to_host(t["mv_z_sym"], *t["mv_dp"]["sym"], *t["mv_dp"]["idx"],
+                                   t["z_sym"], *t["y_dp"]["sym"], *t["y_dp"]["idx"]))
+        out = None
+        if want_dpb:
+            out = {
+                "ref_frame": self._export(B, t["x_hat"], clamp=(0.0, 1.0) if clamp_ref else None),
+                "ref_feature": self._export(B, t["feature"]),
+                "ref_y": self._export(B, t["y_hat"]),
+                "ref_mv_y": self._export(B, t["mv_y_hat"]),
+            }
+        return host, out
+
+    def encode_symbols(self, host):
+        """Host half of compress(): the sequential rANS coder (GIL released inside).  Stream order:
+        z_mv, mv_y pass 0/1, z, y pass 0/1 (video_model.py:333-340)."""
+        rt = self._need_coder()
         mv_z, ms0, ms1, mi0, mi1, z, ys0, ys1, yi0, yi1 = host
         c = rt.coder
         c.reset_encoder()
@@ -446,20 +463,17 @@ class DMC(CompressionModel):
         c.encode_channels(z, rt.tables["bit_estimator_z"])
         c.encode_planes(ys0, yi0, rt.tables["y"])
         c.encode_planes(ys1, yi1, rt.tables["y"])
-        bit_stream = c.flush_encoder()
+        return c.flush_encoder()
+
+    @torch.no_grad()
+    def compress(self, x, dpb, mv_y_q_scale, y_q_scale, _want_dpb=True):
+        """video_model.py:263-352."""
+        host, dbp = self.compress_symbols(x, dpb, mv_y_q_scale, y_q_scale, want_dpb=_want_dpb)
+        bit_stream = self.encode_symbols(host)
+        mv_z, ms0, ms1, mi0, mi1, z, ys0, ys1, yi0, yi1 = host
         self._last_symbols = dict(mv_z=mv_z, mv_y_q_w_0=ms0, mv_y_q_w_1=ms1, mv_idx_0=mi0, mv_idx_1=mi1,
                                   z=z, y_q_w_0=ys0, y_q_w_1=ys1, y_idx_0=yi0, y_idx_1=yi1)
-        if not _want_dpb:      # encode_decode() only uses the decoder's reconstruction
-            return {"dbp": None, "bit_stream": bit_stream}
-        return {
-            "dbp": {
-                "ref_frame": self._export(B, t["x_hat"]),
-                "ref_feature": self._export(B, t["feature"]),
-                "ref_y": self._export(B, t["y_hat"]),
-                "ref_mv_y": self._export(B, t["mv_y_hat"]),
-            },
-            "bit_stream": bit_stream,
-        }
+        return {"dbp": dbp, "bit_stream": bit_stream}   # dbp is None for encode_decode() (decoder's is used)
 
     @torch.no_grad()
     def decompress(self, dpb, string, height, width, mv_y_q_scale, y_q_scale):
