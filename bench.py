@@ -402,9 +402,26 @@ def main():
                 "launches_timed": rf["n_tc"] if use_tc else rf["n"],
                 "conv_share_of_p_frame": {"tc_ms": rf["tc_s"] * 1e3, "all_conv_ms": rf["all_s"] * 1e3,
                                           "all_conv_tflops": rf["all_flop"] / max(rf["all_s"], 1e-9) / 1e12}}
+        top = sorted(rf["by_shape"].items(), key=lambda kv: -kv[1][0])
+        if use_tc and top:
+            # the launch shape that takes most of the frame (3x3 64->64 at 1080p), live-timed here; its DRAM
+            # traffic per launch comes from the committed `ncu --set full` capture of the same shape
+            k0, v0 = top[0]
+            dom = {"shape": k0, "launches": v0[2], "ms_per_launch": v0[0] / v0[2],
+                   "achieved": v0[1] / max(v0[0], 1e-9) / 1e9, "unit": "TFLOP/s",
+                   "frac": v0[1] / max(v0[0], 1e-9) / 1e9 / peak, "traffic": None}
+            try:
+                prof = json.load(open(os.path.join(ROOT, "profiles", "ncu_conv64_halo_r01.json")))[0]
+                mb = lambda key: float(next(v for k, v in prof.items() if k.startswith(key)))   # noqa: E731
+                dom["traffic"] = (mb("dram__bytes_read.sum") + mb("dram__bytes_write.sum")) * 1e6
+                dom["traffic_source"] = "profiles/ncu_conv64_halo_r01.json (3x3 64->64 + residual, 1088x1920)"
+                dom["algorithmic_bytes"] = 3 * 64 * 2 * HP * WP
+            except Exception:
+                pass
+            roof["dominant_launch"] = dom
+            roof["traffic"] = dom["traffic"]
         os.makedirs(os.path.join(ROOT, "gpurun_out"), exist_ok=True)
         with open(os.path.join(ROOT, "gpurun_out", f"conv_by_shape_{a.precision}.json"), "w") as f:
-            top = sorted(rf["by_shape"].items(), key=lambda kv: -kv[1][0])
             json.dump([{"shape": k, "ms": v[0], "tflops": v[1] / max(v[0], 1e-9) / 1e9, "calls": v[2]}
                        for k, v in top], f, indent=1)
         if not a.no_cpu_baseline:

@@ -14,7 +14,7 @@
 // both land 128/64/32-byte swizzled (K-major) in a multi-stage shared-memory ring guarded by
 // full/empty mbarriers.  One elected thread issues CHUNK/16 tcgen05.mma per stage into one of two
 // TMEM accumulator buffers and commits to the stage's empty barrier.  Two epilogue warpgroups
-// (one per accumulator buffer) drain TMEM with tcgen05.ld and run the fused epilogue (bias,
+// (warps 4-7 / 8-11, one per accumulator buffer, setmaxnreg-enlarged register budget) drain TMEM with tcgen05.ld and run the fused epilogue (bias,
 // LeakyReLU, residuals, SE scale, PixelShuffle / channel-slice store, activated twin); residual
 // operands are fetched before the accumulator is awaited so their latency hides behind the MMAs.
 // CTAs are persistent: grid = min(work items, #SM), work items round-robin, N tiles of one spatial
