@@ -161,11 +161,14 @@ def conv_roofline(dmc, intra, x, dpb, q):
         return out
 
     B.conv = timed_conv
+    graphs = dmc._graphs
+    dmc.set_cuda_graphs(False)      # per-launch events need the launches issued one by one
     try:
         dmc.encode_decode_bytes(x, dpb, H, W, q, q)
         torch.cuda.synchronize()
     finally:
         B.conv = orig
+        dmc.set_cuda_graphs(graphs)
     tc_t = sum(e0.elapsed_time(e1) for e0, e1, _, tc, _ in recs if tc) * 1e-3
     tc_f = sum(f for _, _, f, tc, _ in recs if tc)
     all_t = sum(e0.elapsed_time(e1) for e0, e1, _, _, _ in recs) * 1e-3
@@ -214,6 +217,8 @@ def main():
     ap.add_argument("--precision", default=os.environ.get("VCM_B200_PRECISION", "bf16"))
     ap.add_argument("--impl", default="b200")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--cuda-graphs", type=int, default=1,
+                    help="replay each frame's launch sequence from captured CUDA graphs (vcm_ts_b200/graphs.py)")
     ap.add_argument("--seqs-per-gpu", type=int, default=8,
                     help="independent sequences coded concurrently per GPU (own thread + CUDA stream each): "
                          "while one sequence's symbols are in the host rANS coder the other's convs run")
@@ -224,7 +229,8 @@ def main():
     gop = a.gop
     cfg = {"workload": f"DCVC-HEM GOP-{gop} 1080p (1920x1088 padded) sequence encode+decode per GPU: "
                        f"1 I-frame (IntraNoAR) + {gop - 1} P-frames (DMC), real rANS bitstreams",
-           "gop": gop, "sequences_per_gpu": a.seqs_per_gpu, "precision": a.precision, "parallelism": f"seq-shard x{world}",
+           "gop": gop, "sequences_per_gpu": a.seqs_per_gpu, "precision": a.precision,
+           "cuda_graphs": bool(a.cuda_graphs), "parallelism": f"seq-shard x{world}",
            "weights": "random init (reference init, conv x0.7)",
            "l2": "working set per frame >> 126 MB L2 (1080p activations), no explicit flush"}
     sd_p, sd_i = make_state_dicts(0)
@@ -274,6 +280,7 @@ def main():
         dmc_k, intra_k = dmc_k.to(dev), intra_k.to(dev)
         dmc_k.update(force=True)
         intra_k.update(force=True)
+        dmc_k.set_cuda_graphs(bool(a.cuda_graphs))
         # 8-bit frames, as video is: uint8 HWC in pinned host memory for the e2e arm, and the same
         # frames normalised + padded on the device for the resident arm
         from vcm_ts_b200 import frame_io
@@ -372,7 +379,8 @@ def main():
         w0, w1 = workers[0], workers[1]
         pipe = GopPipeline((w1["dmc"], w1["intra"]), (w0["dmc"], w0["intra"]), dev)
         frames = [w0["seq_dev"][t:t + 1] for t in range(n1)]
-        pipe.code_gop(frames[:3], H, W, q, q, q)
+        for _ in range(2):      # eager pass, then the pass that captures the encoder-chain graphs
+            pipe.code_gop(frames[:4], H, W, q, q, q)
         torch.cuda.synchronize()
         t0 = time.time()
         pipe.code_gop(frames, H, W, q, q, q)

@@ -92,9 +92,13 @@ class EmulBackend:
         self._store(out, t)
         return out
 
-    def to_nchw(self, v, clamp=None):
+    def to_nchw(self, v, clamp=None, out=None):
         t = self._nchw(v).contiguous()
-        return t.clamp(*clamp) if clamp is not None else t
+        t = t.clamp(*clamp) if clamp is not None else t
+        if out is not None:
+            out.copy_(t)
+            return out
+        return t
 
     def copy(self, src, dst):
         dst.dense().copy_(src.dense().to(dst.dtype))

@@ -319,3 +319,59 @@ def test_gop_pipeline_equals_serial_coding(precision):
         assert blobs == want_blobs
         for t in range(5):
             assert torch.equal(got_rec[t], want_rec[t]), t
+
+
+@pytest.mark.parametrize("precision", ["bf16", "fp32"])
+def test_cuda_graph_mode_equals_eager_coding(precision):
+    """set_cuda_graphs(True): the per-frame launch sequences are captured (graphs.py) and replayed.
+    Containers and reconstructions must be byte-identical to eager coding -- serial per-frame calls
+    and the overlapped GopPipeline -- across three GOPs (eager pass, capture pass, pure replay)."""
+    from oracle import fixture
+    from vcm_ts_b200.pipeline import GopPipeline
+    dev = "cuda:0"
+    fr = fixture.fixture_frames(128, 192, 5, seed=11).to(dev)
+
+    def serial(dmc, intra):
+        blobs, recs = [], []
+        r, blob = intra.encode_decode_bytes(fr[0:1], 1.0, 128, 192)
+        blobs.append(blob)
+        recs.append(r["x_hat"].clone())
+        dpb = {"ref_frame": r["x_hat"], "ref_feature": None, "ref_y": None, "ref_mv_y": None}
+        for t in range(1, 5):
+            r, blob = dmc.encode_decode_bytes(fr[t:t + 1], dpb, 128, 192, 1.0, 1.0)
+            dpb = r["dpb"]
+            blobs.append(blob)
+            recs.append(dpb["ref_frame"].clone())
+        return blobs, recs
+
+    want_blobs, want_rec = serial(*_models(precision))
+    dmc, intra = _models(precision)
+    dmc.set_cuda_graphs(True)
+    s = torch.cuda.Stream(dev)
+    with torch.cuda.stream(s):
+        for gop in range(3):
+            blobs, recs = serial(dmc, intra)
+            s.synchronize()
+            assert blobs == want_blobs, gop
+            for t in range(5):
+                assert torch.equal(recs[t], want_rec[t]), (gop, t)
+    B = dmc._rt.B
+    assert B.graph_replays > 0 and len(dmc._rt.programs.progs) == 4   # enc/dec x first/steady P-frame
+    # also from the legacy default stream (capture runs on a side stream)
+    blobs, recs = serial(dmc, intra)
+    assert blobs == want_blobs and all(torch.equal(a, b) for a, b in zip(recs, want_rec))
+
+    enc, dec = _models(precision), _models(precision)
+    enc[0].set_cuda_graphs(True)
+    dec[0].set_cuda_graphs(True)
+    pipe = GopPipeline(enc, dec, dev)
+    got = {}
+    for gop in range(3):
+        got.clear()
+        blobs = pipe.code_gop([fr[t:t + 1] for t in range(5)], 128, 192, 1.0, 1.0, 1.0,
+                              on_recon=lambda t, x: got.__setitem__(t, x.clone()))
+        torch.cuda.synchronize()
+        assert blobs == want_blobs, gop
+        for t in range(5):
+            assert torch.equal(got[t], want_rec[t]), (gop, t)
+    assert enc[0]._rt.B.graph_replays > 0 and dec[0]._rt.B.graph_replays > 0

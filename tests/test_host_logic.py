@@ -124,3 +124,69 @@ def test_no_cpu_path_in_product():
     x = torch.rand(1, 3, 64, 64)
     with pytest.raises(RuntimeError):
         m.forward_one_frame(x, {"ref_frame": x, "ref_feature": None, "ref_y": None, "ref_mv_y": None}, 1.0, 1.0)
+
+
+class _EagerPrograms:
+    """graphs.ProgramCache stand-in for CPU: every call runs the frame body directly.  What is left
+    of the CUDA-graph mode is its static, overwritten-in-place frame state (models.py `_statics`)."""
+
+    def __init__(self, device):
+        self.device, self.keys = device, []
+
+    def run(self, key, make_gen, service):
+        from vcm_ts_b200.graphs import drive_eager
+        self.keys.append(key)
+        return drive_eager(make_gen(), service, self.device)
+
+
+def test_static_frame_state_of_graph_mode_matches_plain_mode(models, golden_dir):
+    """set_cuda_graphs(True): dpb entries are static buffers read and then overwritten in place by
+    every frame.  Same bitstreams and reconstructions as the plain mode, for the serial
+    encode_decode chain, for the encoder-side chain of pipeline.py, and when a caller hands in
+    foreign tensors."""
+    dmc, intra = models
+    G = np.load(os.path.join(golden_dir, "tiny_64x128.npz"))
+    ph, pw, qi, qmv, qy = G["meta"]
+    ph, pw = int(ph), int(pw)
+    fr = torch.from_numpy(G["frames_u8"])
+    xs = [_pad64(fr[t:t + 1].float() / 255.0) for t in range(fr.shape[0])]
+    rec0 = intra.encode_decode_bytes(xs[0], qi, ph, pw)[0]["x_hat"]
+    first = {"ref_frame": rec0, "ref_feature": None, "ref_y": None, "ref_mv_y": None}
+    mvq, _ = O.get_rounded_q(qmv)
+    yq, _ = O.get_rounded_q(qy)
+
+    from vcm_ts_b200.stream_helper import unpack_p
+
+    def run(static):
+        dmc.set_cuda_graphs(static)
+        blobs, recs, enc_recs = [], [], []
+        dpb, edpb = dict(first), dict(first)
+        for x in xs[1:]:
+            r, blob = dmc.encode_decode_bytes(x, dpb, ph, pw, qmv, qy)
+            dpb = r["dpb"]
+            blobs.append(blob)
+            recs.append(dpb["ref_frame"].clone())
+            host, edpb = dmc.compress_symbols(x, edpb, mvq, yq, want_dpb=True, clamp_ref=True)
+            assert dmc.encode_symbols(host) == unpack_p(blob)[2]
+            enc_recs.append(edpb["ref_frame"].clone())
+        return blobs, recs, enc_recs
+
+    try:
+        want = run(False)
+        dmc._rt.programs = _EagerPrograms(dmc._rt.B.device)
+        got = run(True)
+        keys = dmc._rt.programs.keys
+        # second GOP with a foreign (cloned) ref_frame: copied into the static buffer
+        got2 = run(True)
+    finally:
+        dmc.set_cuda_graphs(False)
+    for a, b in ((want, got), (want, got2)):
+        assert a[0] == b[0]
+        for u, v in zip(a[1] + a[2], b[1] + b[2]):
+            assert torch.equal(u, v)
+    # the encoder's own reconstruction equals the decoder's (what pipeline.py relies on)
+    for u, v in zip(want[1], want[2]):
+        assert torch.equal(u, v)
+    # first P-frame and steady-state frames select different programs; steady frames share one
+    enc_keys = [k for k in keys if k[0] == "enc"]
+    assert len(set(keys)) < len(keys) and len(set(enc_keys)) >= 3

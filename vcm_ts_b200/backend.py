@@ -79,7 +79,8 @@ class CudaBackend:
         # bf16 mode: producers also store the activated twin a following ResBlock reads, so the
         # tensor-core engine never needs a pre-activation on TMA-loaded tiles
         self.use_twin = precision == "bf16"
-        self.launches = 0
+        self.launches = 0          # kernels launched (graph replays add their kernel count)
+        self.graph_replays = 0
 
     # -- plumbing -------------------------------------------------------------------------
     @property
@@ -193,8 +194,10 @@ class CudaBackend:
         self.launches += 1
         return out
 
-    def to_nchw(self, v, clamp=None):
-        out = torch.empty((v.N, v.C, v.H, v.W), dtype=torch.float32, device=self.device)
+    def to_nchw(self, v, clamp=None, out=None):
+        if out is None:
+            out = torch.empty((v.N, v.C, v.H, v.W), dtype=torch.float32, device=self.device)
+        assert tuple(out.shape) == (v.N, v.C, v.H, v.W) and out.dtype == torch.float32 and out.is_contiguous()
         lo, hi = clamp if clamp is not None else (0.0, 0.0)
         check(self.L.vcm_nhwc_to_nchw(v.ptr, out.data_ptr(), v.N, v.C, v.H, v.W, v.cs, _code(v.dtype),
                                       1 if clamp is not None else 0, lo, hi, self.stream),

@@ -22,6 +22,7 @@ from torch import nn
 
 from . import arch
 from .backend import CudaBackend, View
+from .graphs import ProgramCache, drive_eager
 from .entropy import CdfTables, RansCoder, ScaleIndexTable, factorized_tables
 from .nets import Graph
 from .stream_helper import (decode_i, decode_p, encode_i, encode_p, filesize, get_downsampled_shape,
@@ -44,6 +45,10 @@ class _Runtime:
         self.persist = {}
         self.coder = None
         self.tables = {}
+        self.qcache = {}
+        self.statics = {}
+        self.static_ids = {}
+        self.programs = ProgramCache(backend)
 
 
 class CompressionModel(nn.Module):
@@ -54,6 +59,7 @@ class CompressionModel(nn.Module):
         self.y_distribution = y_distribution
         self._precision = precision or os.environ.get("VCM_B200_PRECISION", "fp32")
         self._rt = None
+        self._graphs = os.environ.get("VCM_B200_CUDA_GRAPHS", "0") == "1"
         self._backend_factory = None          # tests inject an emulation backend here
         self.entropy_coder = None             # reference attribute; set by update()
         self._scale_table = ScaleIndexTable(y_distribution)
@@ -104,6 +110,15 @@ class CompressionModel(nn.Module):
     def set_precision(self, precision):
         if precision != self._precision:
             self._precision, self._rt = precision, None
+        return self
+
+    def set_cuda_graphs(self, enabled=True):
+        """Opt-in: capture the per-frame launch sequences of compress / decompress into CUDA graphs
+        (graphs.py).  In this mode the returned dpb is a set of STATIC buffers owned by the model
+        (ref_frame an NCHW fp32 tensor as usual, ref_feature / ref_y / ref_mv_y internal NHWC views):
+        the next call overwrites them in place, so use them (or copy them) before coding the next
+        frame.  Symbols, bitstreams and reconstructions are identical to the eager mode."""
+        self._graphs = bool(enabled)
         return self
 
     @property
@@ -192,6 +207,12 @@ class CompressionModel(nn.Module):
     # ---- q helpers ------------------------------------------------------------------------
     def _curr_q(self, rt, basic, q_scale, N):
         """LowerBound(q_basic, .5) * q_scale -> contiguous [N, C] fp32 on the device."""
+        if not torch.is_tensor(q_scale):
+            key = (id(basic), basic._version, basic.data_ptr(), float(q_scale), N)
+            hit = rt.qcache.get(key)
+            if hit is None:
+                hit = rt.qcache[key] = self._curr_q(rt, basic, torch.tensor(float(q_scale)), N)
+            return hit
         qb = torch.max(basic.detach(), torch.ones_like(basic) * 0.5)
         if torch.is_tensor(q_scale):
             q = qb * q_scale.detach().to(qb.device, qb.dtype)
@@ -215,13 +236,23 @@ class CompressionModel(nn.Module):
 
     @staticmethod
     def _import(B, t, dtype=None):
-        """NCHW tensor from a caller -> NHWC view (cached twin if still valid)."""
+        """NCHW tensor from a caller -> NHWC view (cached twin if still valid).  Internal dpb entries
+        (set_cuda_graphs) already are views."""
+        if isinstance(t, View):
+            return t
         hit = getattr(t, "_vcm_view", None)
         want = dtype or B.act_dtype
         if hit is not None and hit[1] == t._version and hit[0].dtype == want and \
                 hit[0].t.device == B.device and (hit[0].N, hit[0].C, hit[0].H, hit[0].W) == tuple(t.shape):
             return hit[0]
         return B.from_nchw(t, dtype=dtype)
+
+    @staticmethod
+    def _dpb_into(B, entry, out):
+        """Previous-frame latent (NCHW tensor from a caller, or an internal view) -> channel slice."""
+        if isinstance(entry, View):
+            return B.copy(entry, out)
+        return B.from_nchw(entry, out=out)
 
     # ---- host <-> device symbol traffic -----------------------------------------------------
     @staticmethod
@@ -342,7 +373,7 @@ class DMC(CompressionModel):
         fin = B.new(N, h, w, 192, zero=dpb["ref_mv_y"] is None)
         g.hyper_synthesis("mv_hyper_prior_decoder", mv_z_hat, out=fin.sl(0, 128))
         if dpb["ref_mv_y"] is not None:
-            B.from_nchw(dpb["ref_mv_y"], out=fin.sl(128, 192))
+            self._dpb_into(B, dpb["ref_mv_y"], fin.sl(128, 192))
         return g.three_convs("mv_y_prior_fusion", fin)
 
     def _y_prior(self, rt, z_hat, e3, dpb):
@@ -354,7 +385,7 @@ class DMC(CompressionModel):
         g.conv("temporal_prior_encoder.2", t, stride=2, out=fin.sl(0, 192))
         g.hyper_synthesis("contextual_hyper_prior_decoder", z_hat, out=fin.sl(192, 384))
         if dpb["ref_y"] is not None:
-            B.from_nchw(dpb["ref_y"], out=fin.sl(384, 480))
+            self._dpb_into(B, dpb["ref_y"], fin.sl(384, 480))
         return g.three_convs("y_prior_fusion", fin)
 
     def _contextual_encoder(self, rt, ctx, e2, e3):
@@ -371,7 +402,7 @@ class DMC(CompressionModel):
         f = g.conv(n + ".conv3", f, stride=2)
         return g.conv(n + ".conv4", f, stride=2)
 
-    def _reconstruct(self, rt, y_hat, ctx, e2, e3):
+    def _reconstruct(self, rt, y_hat, ctx, e2, e3, feature_out=None):
         """ContextualDecoder (video_model.py:93-112) + ReconGeneration (:115-128)."""
         g = rt.graph
         n = "contextual_decoder"
@@ -385,19 +416,22 @@ class DMC(CompressionModel):
         n = "recon_generation_net"
         f = g.conv(n + ".first_conv", ctx.sl(0, 96))
         f = g.unet(n + ".unet_1", f)
-        feature = g.unet(n + ".unet_2", f)
+        feature = g.unet(n + ".unet_2", f, out=feature_out)
         x_hat = g.conv(n + ".recon_conv", feature, out_dtype=F32)
         return feature, x_hat
 
-    def _analyse(self, x, dpb, mv_y_q_scale, y_q_scale, want_full):
+    def _analyse(self, x, dpb, mv_y_q_scale, y_q_scale, want_full, outs=None):
         """Encoder-side trunk shared by compress() and forward_one_frame() (video_model.py:263-331 /
-        :470-538)."""
+        :470-538).  outs: static next-frame buffers (`_statics`) that mv_y_hat / y_hat / feature are
+        written to in place of fresh tensors (each is read, as the previous frame's, before the
+        kernel that overwrites it)."""
         rt = self._runtime()
         g, B = rt.graph, rt.B
         N, _, H, W = x.shape
         q_mv = self._curr_q(rt, self.mv_y_q_basic, mv_y_q_scale, N)
         q_y = self._curr_q(rt, self.y_q_basic, y_q_scale, N)
         table = self._scale_table
+        outs = outs or {}
 
         est_mv = g.spynet("optic_flow", x, dpb["ref_frame"])
         mv_y = B.scale(g.analysis("mv_encoder", est_mv), q_mv, "div")
@@ -406,7 +440,8 @@ class DMC(CompressionModel):
         mv_z_sym = B.empty(zs, torch.int16)
         mv_z_hat = B.round_latent(mv_z, sym=mv_z_sym)
         mv_fusion = self._mv_prior(rt, mv_z_hat, dpb)
-        mv_dp = g.dual_prior_encode(table, mv_y, mv_fusion, "mv_y_spatial_prior", q_mv, want_full)
+        mv_dp = g.dual_prior_encode(table, mv_y, mv_fusion, "mv_y_spatial_prior", q_mv, want_full,
+                                    y_hat=outs.get("ref_mv_y"))
         mv_y_hat = mv_dp["y_hat"]
         mv_hat = g.synthesis("mv_decoder", mv_y_hat, out_dtype=F32)
 
@@ -420,12 +455,69 @@ class DMC(CompressionModel):
         z_sym = B.empty(zs, torch.int16)
         z_hat = B.round_latent(z, sym=z_sym)
         y_fusion = self._y_prior(rt, z_hat, e3, dpb)
-        y_dp = g.dual_prior_encode(table, y, y_fusion, "y_spatial_prior", q_y, want_full)
+        y_dp = g.dual_prior_encode(table, y, y_fusion, "y_spatial_prior", q_y, want_full,
+                                   y_hat=outs.get("ref_y"))
         y_hat = y_dp["y_hat"]
-        feature, x_hat = self._reconstruct(rt, y_hat, ctx, e2, e3)
+        feature, x_hat = self._reconstruct(rt, y_hat, ctx, e2, e3, outs.get("ref_feature"))
         return dict(mv_z_sym=mv_z_sym, z_sym=z_sym, mv_z_hat=mv_z_hat, z_hat=z_hat, mv_dp=mv_dp, y_dp=y_dp,
                     mv_y_hat=mv_y_hat, y_hat=y_hat, feature=feature, x_hat=x_hat, warp_frame=warp_frame,
                     est_mv=est_mv, mv_hat=mv_hat)
+
+    # ---- static next-frame state + captured programs (set_cuda_graphs) ---------------------------
+    def _statics(self, rt, H, W, side):
+        """Fixed-address frame state for the captured programs of one side ("enc" / "dec"): the
+        current frame / first latent, and the four dpb entries, which every coded frame reads (as the
+        previous frame's) and then overwrites.  The two sides keep separate chains, so
+        compress(dpb) followed by decompress(dpb) on one model still sees the same `dpb`."""
+        st = rt.statics.get((H, W, side))
+        if st is None:
+            B = rt.B
+            st = {"ref_frame": torch.empty((1, 3, H, W), dtype=F32, device=B.device),
+                  "ref_feature": B.new(1, H, W, 64),
+                  "ref_y": B.new(1, H // 16, W // 16, 96),
+                  "ref_mv_y": B.new(1, H // 16, W // 16, 64)}
+            for k, v in st.items():
+                rt.static_ids[id(v)] = (side, k)
+            if side == "enc":
+                st["x"] = torch.empty((1, 3, H, W), dtype=F32, device=B.device)
+            else:
+                st["mv_z_sym"] = B.empty((1, 64, H // 64, W // 64), torch.int16)
+            rt.statics[(H, W, side)] = st
+        return st
+
+    def _load_statics(self, rt, st, dpb, side):
+        """dpb from the caller -> the dpb the frame body reads.  Entries that are static buffers of
+        this model (the dpb it returned for the previous frame, either side) are read where they
+        lie; anything else is copied into `st`.  Also returns the pattern that selects the program."""
+        B = rt.B
+        inner, pattern = {}, []
+        for k in ("ref_frame", "ref_feature", "ref_y", "ref_mv_y"):
+            v = dpb[k]
+            if v is None:
+                inner[k] = None
+                pattern.append(None)
+                continue
+            owner = rt.static_ids.get(id(v))
+            if owner is not None and owner[1] == k:
+                inner[k] = v
+                pattern.append(owner[0])
+                continue
+            if k == "ref_frame":
+                st[k].copy_(v.detach().to(B.device, F32))
+            else:
+                B.copy(self._import(B, v), st[k])
+            inner[k] = st[k]
+            pattern.append(side)
+        return inner, tuple(pattern)
+
+    def _enc_body(self, rt, x, dpb, q_mv, q_y, outs, clamp_ref):
+        """Generator with no host hand-off (graphs.py): one captured graph."""
+        t = self._analyse(x, dpb, q_mv, q_y, False, outs)
+        if outs is not None:
+            rt.B.to_nchw(t["x_hat"], clamp=(0.0, 1.0) if clamp_ref else None, out=outs["ref_frame"])
+        return (t["mv_z_sym"], *t["mv_dp"]["sym"], *t["mv_dp"]["idx"],
+                t["z_sym"], *t["y_dp"]["sym"], *t["y_dp"]["idx"])
+        yield   # noqa: unreachable -- makes this a generator
 
     # ---- public API ------------------------------------------------------------------------------
     @torch.no_grad()
@@ -437,6 +529,17 @@ class DMC(CompressionModel):
         rt = self._need_coder()
         assert x.shape[0] == 1, "the bitstream path is batch 1 (entropy_models.py:186)"
         B = rt.B
+        if self._graphs:
+            H, W = x.shape[2:]
+            st = self._statics(rt, H, W, "enc")
+            inner, pattern = self._load_statics(rt, st, dpb, "enc")
+            st["x"].copy_(x.detach().to(B.device, F32))
+            outs = st if want_dpb else None
+            key = ("enc", H, W, pattern, float(mv_y_q_scale), float(y_q_scale), want_dpb, clamp_ref)
+            syms = rt.programs.run(key, lambda: self._enc_body(rt, st["x"], inner, float(mv_y_q_scale),
+                                                                float(y_q_scale), outs, clamp_ref), None)
+            out = {k: st[k] for k in ("ref_frame", "ref_feature", "ref_y", "ref_mv_y")} if want_dpb else None
+            return tuple(self._to_host(*syms)), out
         t = self._analyse(x, dpb, mv_y_q_scale, y_q_scale, want_full=False)
         host = tuple(self._to_host(t["mv_z_sym"], *t["mv_dp"]["sym"], *t["mv_dp"]["idx"],
                                    t["z_sym"], *t["y_dp"]["sym"], *t["y_dp"]["idx"]))
@@ -475,27 +578,74 @@ class DMC(CompressionModel):
                                   z=z, y_q_w_0=ys0, y_q_w_1=ys1, y_idx_0=yi0, y_idx_1=yi1)
         return {"dbp": dbp, "bit_stream": bit_stream}   # dbp is None for encode_decode() (decoder's is used)
 
+    def _dec_body(self, rt, dpb, q_mv_scale, q_y_scale, zs, outs):
+        """Decoder frame body (video_model.py:354-422) as a generator: yields the host-coder requests
+        of graphs.py (two latents, four index planes), returns (x_hat, feature, y_hat, mv_y_hat)."""
+        g, B = rt.graph, rt.B
+        q_mv = self._curr_q(rt, self.mv_y_q_basic, q_mv_scale, 1)
+        q_y = self._curr_q(rt, self.y_q_basic, q_y_scale, 1)
+        table = self._scale_table
+        outs = outs or {}
+
+        def planes(gen):
+            try:
+                idx = next(gen)
+                while True:
+                    sym = yield ("plane", idx)
+                    idx = gen.send(sym)
+            except StopIteration as e:
+                return e.value
+
+        mv_z_hat = B.symbols_to_latent(outs["mv_z_sym"], 1, zs[0], zs[1], 64)
+        mv_fusion = self._mv_prior(rt, mv_z_hat, dpb)
+        mv_y_hat = yield from planes(g.dual_prior_decode_gen(table, mv_fusion, 64, "mv_y_spatial_prior",
+                                                             q_mv, y_hat=outs.get("ref_mv_y")))
+        mv_hat = g.synthesis("mv_decoder", mv_y_hat, out_dtype=F32)
+        ctx, e2, e3, _ = self.motion_compensation(dpb, mv_hat)
+        z_sym = yield ("z", "bit_estimator_z", 64, zs)
+        z_hat = B.symbols_to_latent(z_sym, 1, zs[0], zs[1], 64)
+        y_fusion = self._y_prior(rt, z_hat, e3, dpb)
+        y_hat = yield from planes(g.dual_prior_decode_gen(table, y_fusion, 96, "y_spatial_prior", q_y,
+                                                          y_hat=outs.get("ref_y")))
+        feature, x_hat = self._reconstruct(rt, y_hat, ctx, e2, e3, outs.get("ref_feature"))
+        if "ref_frame" in outs:
+            B.to_nchw(x_hat, clamp=(0.0, 1.0), out=outs["ref_frame"])
+        return x_hat, feature, y_hat, mv_y_hat
+
+    def _dec_service(self, rt):
+        """Host side of the decoder requests: the sequential rANS decoder (GIL released inside)."""
+        def service(req):
+            if req[0] == "plane":
+                idx = req[1].cpu()
+                out = torch.empty(idx.shape, dtype=torch.int16)
+                rt.coder.decode_planes(idx, rt.tables["y"], out)
+                return out
+            _, name, C, zs = req
+            out = torch.empty((1, C, zs[0], zs[1]), dtype=torch.int16)
+            rt.coder.decode_channels(C, zs[0] * zs[1], rt.tables[name], out)
+            return out
+        return service
+
     @torch.no_grad()
     def decompress(self, dpb, string, height, width, mv_y_q_scale, y_q_scale):
         """video_model.py:354-422."""
         rt = self._need_coder()
-        g, B = rt.graph, rt.B
-        q_mv = self._curr_q(rt, self.mv_y_q_basic, mv_y_q_scale, 1)
-        q_y = self._curr_q(rt, self.y_q_basic, y_q_scale, 1)
-        table = self._scale_table
+        B = rt.B
         rt.coder.set_stream(string)
         zs = get_downsampled_shape(height, width, 64)
-        dec = self._decode_plane_fn(rt)
-
-        mv_z_hat = self._decode_z(rt, "bit_estimator_z_mv", 64, zs)
-        mv_fusion = self._mv_prior(rt, mv_z_hat, dpb)
-        mv_y_hat = g.dual_prior_decode(table, mv_fusion, 64, "mv_y_spatial_prior", q_mv, dec)
-        mv_hat = g.synthesis("mv_decoder", mv_y_hat, out_dtype=F32)
-        ctx, e2, e3, _ = self.motion_compensation(dpb, mv_hat)
-        z_hat = self._decode_z(rt, "bit_estimator_z", 64, zs)
-        y_fusion = self._y_prior(rt, z_hat, e3, dpb)
-        y_hat = g.dual_prior_decode(table, y_fusion, 96, "y_spatial_prior", q_y, dec)
-        feature, x_hat = self._reconstruct(rt, y_hat, ctx, e2, e3)
+        service = self._dec_service(rt)
+        mv_z = service(("z", "bit_estimator_z_mv", 64, zs))      # first in the stream, no device input
+        if self._graphs:
+            H, W = zs[0] * 64, zs[1] * 64
+            st = self._statics(rt, H, W, "dec")
+            inner, pattern = self._load_statics(rt, st, dpb, "dec")
+            st["mv_z_sym"].copy_(mv_z)
+            key = ("dec", H, W, pattern, float(mv_y_q_scale), float(y_q_scale))
+            rt.programs.run(key, lambda: self._dec_body(rt, inner, float(mv_y_q_scale), float(y_q_scale),
+                                                        zs, st), service)
+            return {"dpb": {k: st[k] for k in ("ref_frame", "ref_feature", "ref_y", "ref_mv_y")}}
+        gen = self._dec_body(rt, dpb, mv_y_q_scale, y_q_scale, zs, {"mv_z_sym": mv_z.to(B.device)})
+        x_hat, feature, y_hat, mv_y_hat = drive_eager(gen, service, B.device)
         return {
             "dpb": {
                 "ref_frame": self._export(B, x_hat, clamp=(0.0, 1.0)),

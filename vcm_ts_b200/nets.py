@@ -182,10 +182,10 @@ class Graph:
         return flow
 
     # ---- common_model.py:104-180 (forward_dual_prior / compress_dual_prior), both passes
-    def dual_prior_encode(self, table, y, fusion, prior_pre, q_outer, want_full=False):
+    def dual_prior_encode(self, table, y, fusion, prior_pre, q_outer, want_full=False, y_hat=None):
         """y: latent / outer q; fusion: (q_step, scales, means) view.  Returns dict with the two
-        symbol planes, two index planes, y_hat (already * q_step * q_outer) and, if want_full,
-        y_q / scales_hat for the likelihood kernel."""
+        symbol planes, two index planes, y_hat (already * q_step * q_outer; written to `y_hat` when
+        given) and, if want_full, y_q / scales_hat for the likelihood kernel."""
         B = self.B
         N, h, w, C = y.N, y.H, y.W, y.C
         params = B.new(N, h, w, 4 * C, dtype=y.dtype)
@@ -198,26 +198,41 @@ class Graph:
         B.dp_pass0(0, table, fusion, params, C, y=y, yq=yq, sym=sym0, idx=idx0, y_q_full=yqf,
                    scales_full=scf)
         prior = self.three_convs(prior_pre, params)
-        y_hat = B.new(N, h, w, C, dtype=y.dtype)
+        if y_hat is None:
+            y_hat = B.new(N, h, w, C, dtype=y.dtype)
         B.dp_pass1(0, table, fusion, prior, params, C, q_outer=q_outer, y_hat=y_hat, yq=yq, sym=sym1,
                    idx=idx1, y_q_full=yqf, scales_full=scf)
         return dict(sym=(sym0, sym1), idx=(idx0, idx1), y_hat=y_hat, y_q=yqf, scales_hat=scf)
 
     # ---- common_model.py:182-217 (decompress_dual_prior)
-    def dual_prior_decode(self, table, fusion, C, prior_pre, q_outer, decode_plane):
-        """decode_plane(idx uint8 device tensor [N,C/2,h,w]) -> int16 device tensor of symbols."""
+    def dual_prior_decode_gen(self, table, fusion, C, prior_pre, q_outer, y_hat=None):
+        """Generator form: yields each uint8 index plane [N,C/2,h,w] (device) and is sent back the
+        int16 symbol plane (device) the host coder decoded for it; returns y_hat.  The two yields are
+        the only host hand-offs, so the device work between them can be captured in CUDA graphs
+        (graphs.py)."""
         B = self.B
         N, h, w = fusion.N, fusion.H, fusion.W
         params = B.new(N, h, w, 4 * C, dtype=fusion.dtype)
         plane = (N, C // 2, h, w)
         idx = B.empty(plane, torch.uint8)
         B.dp_pass0(1, table, fusion, params, C, idx=idx)
-        sym = decode_plane(idx)
+        sym = yield idx
         B.dp_pass0(2, table, fusion, params, C, sym=sym)
         prior = self.three_convs(prior_pre, params)
         idx = B.empty(plane, torch.uint8)
         B.dp_pass1(1, table, fusion, prior, params, C, idx=idx)
-        sym = decode_plane(idx)
-        y_hat = B.new(N, h, w, C, dtype=fusion.dtype)
+        sym = yield idx
+        if y_hat is None:
+            y_hat = B.new(N, h, w, C, dtype=fusion.dtype)
         B.dp_pass1(2, table, fusion, prior, params, C, q_outer=q_outer, y_hat=y_hat, sym=sym)
         return y_hat
+
+    def dual_prior_decode(self, table, fusion, C, prior_pre, q_outer, decode_plane):
+        """decode_plane(idx uint8 device tensor [N,C/2,h,w]) -> int16 device tensor of symbols."""
+        gen = self.dual_prior_decode_gen(table, fusion, C, prior_pre, q_outer)
+        try:
+            idx = next(gen)
+            while True:
+                idx = gen.send(decode_plane(idx))
+        except StopIteration as e:
+            return e.value
