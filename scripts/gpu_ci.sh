@@ -17,7 +17,7 @@ for s in $STAGES; do case $s in
   e2e_fp32) run e2e_fp32 300 python -m pytest tests/test_gpu_e2e.py -m gpu -q -s -k "fp32 or batched" ;;
   e2e_bf16) run e2e_bf16 200 python -m pytest tests/test_gpu_e2e.py -m gpu -q -s -k "bf16 or 1080p or pipeline" ;;
   smoke) run smoke 200 python -c "import __graft_entry__ as g; g.smoke()" ;;
-  bench) run bench 400 python bench.py --steps 1 --warmup 1 --gop 8 ;;
+  bench) run bench 400 python bench.py --steps 1 --warmup 2 --gop 8 ;;
   bench_full) run bench_full 1200 python bench.py ;;
   all_gpu) run all_gpu 1500 python -m pytest tests -m gpu -x -q ;;
 esac; done

@@ -231,25 +231,32 @@ __global__ void se_fc_kernel(const float* __restrict__ partial, const float* __r
   }
 }
 
-// Same, with the sum over the nblk partials striped over 256/C thread groups (fixed order: stripe
-// sums, then groups in index order) -- the serial loop above costs ~20 us at 1080p.
-__global__ void __launch_bounds__(256) se_fc_striped_kernel(const float* __restrict__ partial,
-                                                            const float* __restrict__ w1,
-                                                            const float* __restrict__ w2, float* __restrict__ scale,
-                                                            int64_t hw, int C, int Cmid, int nblk) {
+// Same, with the sum over the nblk partials striped over 1024/(C/4) thread groups, each thread
+// adding float4 quarter-rows (fixed order: stripe sums, then groups in index order).  The serial
+// loop above is a chain of ~2000 dependent L2 round trips at 1080p (20-100 us); this one is 32 per
+// thread, eight in flight.
+constexpr int SE_FC_THREADS = 1024;
+__global__ void __launch_bounds__(SE_FC_THREADS) se_fc_striped_kernel(const float* __restrict__ partial,
+                                                                      const float* __restrict__ w1,
+                                                                      const float* __restrict__ w2,
+                                                                      float* __restrict__ scale, int64_t hw, int C,
+                                                                      int Cmid, int nblk) {
   extern __shared__ float sm[];  // part[groups][C] + mean[C] + hid[Cmid]
-  const int groups = 256 / C;
+  const int c4 = C >> 2, groups = SE_FC_THREADS / c4;
   float* part = sm;
   float* mean = sm + groups * C;
   float* hid = mean + C;
   const int n = blockIdx.x;
-  const int c = threadIdx.x % C, grp = threadIdx.x / C;
-  if (grp < groups) {
-    float s = 0.f;
-    const float* p = partial + (int64_t)n * nblk * C + c;
+  const int u = threadIdx.x % c4, grp = threadIdx.x / c4;
+  {
+    float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
+    const float4* p = reinterpret_cast<const float4*>(partial + (int64_t)n * nblk * C) + u;
 #pragma unroll 8
-    for (int b = grp; b < nblk; b += groups) s += __ldg(p + (int64_t)b * C);
-    part[grp * C + c] = s;
+    for (int b = grp; b < nblk; b += groups) {
+      const float4 v = __ldg(p + (int64_t)b * c4);
+      s.x += v.x; s.y += v.y; s.z += v.z; s.w += v.w;
+    }
+    reinterpret_cast<float4*>(part + grp * C)[u] = s;
   }
   __syncthreads();
   if (threadIdx.x < C) {
@@ -424,9 +431,9 @@ extern "C" int vcm_se_scale(const void* x, float* partial, const float* w1, cons
     VCM_DISPATCH_DTYPE(dtype, (se_partial_vec_kernel<T><<<dim3(vblk, N), 256, vrows * C * sizeof(float), s>>>(
                                   (const T*)x, partial, hw, C, cstride, vblk)));
     VCM_CHECK_LAUNCH();
-    if (256 % C == 0) {
-      se_fc_striped_kernel<<<N, 256, ((256 / C) * C + C + Cmid) * sizeof(float), s>>>(partial, w1, w2, scale, hw, C,
-                                                                                     Cmid, vblk);
+    if (C % 4 == 0 && SE_FC_THREADS % (C / 4) == 0 && ((uintptr_t)partial & 15) == 0) {
+      se_fc_striped_kernel<<<N, SE_FC_THREADS, (4 * SE_FC_THREADS + C + Cmid) * sizeof(float), s>>>(
+          partial, w1, w2, scale, hw, C, Cmid, vblk);
     } else {
       se_fc_kernel<<<N, 256, (C + Cmid) * sizeof(float), s>>>(partial, w1, w2, scale, hw, C, Cmid, vblk);
     }

@@ -92,9 +92,12 @@ class ProgramCache:
         B = self.B
         dev = B.device
         cur = torch.cuda.current_stream(dev)
-        if self.side is None:
-            self.side = torch.cuda.Stream(dev)
+        if self.pool is None:
             self.pool = torch.cuda.graph_pool_handle()
+        if self.side is None or self.side.priority != cur.priority:
+            # kernel nodes inherit the capture stream's priority (pipeline.py runs the decoder chain,
+            # the critical path of a single sequence, on a high-priority stream)
+            self.side = torch.cuda.Stream(dev, priority=cur.priority)
         prog = Program(B)
         gen = make_gen()
         reply = None

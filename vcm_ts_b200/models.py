@@ -434,7 +434,15 @@ class DMC(CompressionModel):
         outs = outs or {}
 
         est_mv = g.spynet("optic_flow", x, dpb["ref_frame"])
-        mv_y = B.scale(g.analysis("mv_encoder", est_mv), q_mv, "div")
+        if B.use_twin:
+            # tensor-core mode: the 2-channel flow as bf16 padded to 16 channels (zero weights on the
+            # pad), so the stride-2 first layer of the mv encoder runs on tcgen05 like every other conv
+            mv_in = self._persist(rt, "mv_in", N, H, W, 16, B.act_dtype)
+            B.copy(est_mv, mv_in.sl(0, 2))
+            mv_y = g.analysis("mv_encoder", mv_in, [0, 1] + [-1] * 14)
+        else:
+            mv_y = g.analysis("mv_encoder", est_mv)
+        mv_y = B.scale(mv_y, q_mv, "div")
         mv_z = g.hyper_analysis("mv_hyper_prior_encoder", mv_y)
         zs = (N, 64, mv_z.H, mv_z.W)
         mv_z_sym = B.empty(zs, torch.int16)

@@ -28,8 +28,10 @@ class GopPipeline:
         self.enc_dmc, self.enc_intra = enc_models
         self.dec_dmc, self.dec_intra = dec_models
         self.device = torch.device(device)
+        # the decoder chain (host rANS hand-offs in series with device work) is the critical path of
+        # a single sequence: its kernels take SMs ahead of the encoder's, which runs ahead anyway
         self.s_enc = torch.cuda.Stream(self.device)
-        self.s_dec = torch.cuda.Stream(self.device)
+        self.s_dec = torch.cuda.Stream(self.device, priority=-1)
 
     def code_gop(self, frames, pic_height, pic_width, q_i, q_mv, q_y, on_recon=None):
         """frames: sequence of callables or tensors giving the padded [1,3,Hp,Wp] frame t (called /
