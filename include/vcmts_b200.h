@@ -213,7 +213,8 @@ void vcm_cdf_tables_free(vcm_cdf_tables* t);
 vcm_rans_enc* vcm_rans_enc_new(void);
 void vcm_rans_enc_free(vcm_rans_enc* e);
 void vcm_rans_enc_reset(vcm_rans_enc* e);
-/* symbols int16, per-symbol table index uint8 (scale index)                                 */
+/* symbols int16, per-symbol table index uint8 (scale index).  The encoder keeps pointers into
+   `t` (precomputed per-symbol records): `t` must stay alive until the next flush / reset.       */
 int vcm_rans_enc_push(vcm_rans_enc* e, const int16_t* sym, const uint8_t* idx, int64_t n,
                       const vcm_cdf_tables* t);
 /* symbols int16 laid out [C][hw]; table index = channel (BitEstimator, entropy_models.py:176-187) */

@@ -103,6 +103,66 @@ def test_coder_bytes_equal_reference_cpp():
     assert c.flush_encoder() == want
 
 
+def test_coder_edge_frequencies_division_free_encode_and_mode_fast_path():
+    """The encoder replaces x / freq by a round-up reciprocal and the decoder tries the most probable
+    value first (rans_coder.cpp).  Tables built to hit every special case: freq 1, 2, powers of two
+    and their neighbours, the largest legal freq, a dominant symbol, an escape-heavy table.  Bytes
+    must equal the division-based oracle port (and the reference's own C++ when it is built), and
+    decode back."""
+    rng = np.random.default_rng(11)
+    rows = [
+        [1, 1, 2, 3, 4, 5, 7, 8, 9, 15, 16, 17, 255, 256, 257, 1023, 1024, 1025, 4096, 32768],
+        [65535 - 6, 1, 1, 1, 1, 1, 1],             # dominant symbol (decoder fast path), freq-1 tail
+        [1, 1, 1, 1, 1, 1, 65535 - 6],             # dominant symbol is the escape: fast path must not take it
+        [32768, 16384, 8192, 4096, 2048, 1024, 512, 256, 128, 64, 32, 16, 8, 4, 2, 1],
+        [3] * 200,
+    ]
+    stride = max(len(r) for r in rows) + 1
+    cdf = np.zeros((len(rows), stride), dtype=np.int32)
+    sizes = np.zeros(len(rows), dtype=np.int32)
+    offs = np.array([-3, 0, -2, -8, -100], dtype=np.int32)
+    for i, r in enumerate(rows):
+        f = np.array(r, dtype=np.int64)
+        f[np.argmax(f)] += 65536 - f.sum()         # make the row sum to 2^16 exactly
+        assert f.min() >= 1 and f.sum() == 65536
+        cdf[i, 1:len(r) + 1] = np.cumsum(f)
+        sizes[i] = len(r) + 1
+    n = 60000
+    idx = rng.integers(0, len(rows), n).astype(np.uint8)
+    sym = np.empty(n, dtype=np.int16)
+    for i in range(len(rows)):
+        m = idx == i
+        k = int(m.sum())
+        f = np.diff(cdf[i, :sizes[i]]).astype(np.float64)
+        v = rng.choice(len(f), size=k, p=f / f.sum())          # in-table values by their own probability
+        far = rng.random(k) < 0.05                             # plus out-of-table values on both sides
+        v = np.where(far, rng.integers(-40, len(f) + 40, k), v)
+        sym[m] = (v + offs[i]).astype(np.int16)
+    table = (torch.from_numpy(cdf), torch.from_numpy(sizes), torch.from_numpy(offs))
+    T = CdfTables(*table)
+    c = RansCoder()
+    c.reset_encoder()
+    c.encode_planes(torch.from_numpy(sym), torch.from_numpy(idx), T)
+    mine = c.flush_encoder()
+    o = O.OracleRans()
+    o.reset_encoder()
+    o.encode_with_indexes(sym.astype(np.int32), idx.astype(np.int32), *table)
+    assert mine == o.flush_encoder()
+    from oracle import ref_import
+    try:
+        ref = ref_import.load_ref_native("MLCodec_rans")
+        enc = ref.BufferedRansEncoder()
+        enc.encode_with_indexes(sym.astype(np.int32).tolist(), idx.astype(np.int32).tolist(), cdf.tolist(),
+                                sizes.tolist(), offs.tolist())
+        assert mine == enc.flush()
+    except ImportError:
+        pass
+    c.set_stream(mine)
+    out = torch.empty(n, dtype=torch.int16)
+    c.decode_planes(torch.from_numpy(idx), T, out)
+    assert np.array_equal(out.numpy(), sym)
+
+
 def test_pmf_to_quantized_cdf_matches_oracle():
     rng = np.random.default_rng(3)
     L = _lib.lib()

@@ -10,7 +10,8 @@
 //
 // What is different from the reference is only the plumbing: symbols arrive as int16 and table
 // indexes as uint8 straight from pinned buffers the GPU epilogue wrote (no int32 numpy round
-// trip, no Python list), pending symbols are packed in 32 bits, the decoder finds the symbol with a
+// trip, no Python list), the encoder replaces the per-symbol division by a precomputed round-up
+// reciprocal (exact for every state < 2^63), the decoder tries the most probable value first and else finds the symbol with a
 // 256-bucket lookup + short scan instead of a linear search from 0, and nothing touches Python.
 #include <stdarg.h>
 #include <stdint.h>
@@ -42,15 +43,34 @@ constexpr int32_t kBypassMax = (1 << kBypassBits) - 1;
 constexpr uint64_t kRansL = 1ull << 31;
 }  // namespace
 
+// Encoder record of one (table, value): x -> C(s, x) without a division.  With l = ceil(log2 freq)
+// and rcp = ceil(2^(63+l) / freq) (< 2^64), floor(x / freq) = mulhi(x, rcp) >> (l - 1) for every
+// x < 2^63 (Granlund-Montgomery / Alverson round-up reciprocal, the construction ryg_rans'
+// Rans64EncSymbolInit uses), so
+//     ((x / freq) << 16) + x % freq + start  ==  x + start + q * (2^16 - freq),  q = floor(x / freq).
+// freq == 1: rcp = 2^64 - 1, shift 0 gives q = x - 1, compensated in `bias`.
+struct EncSym {
+  uint64_t rcp;
+  uint32_t bias;       // start (+ 2^16 - 1 when freq == 1)
+  uint16_t freq;       // 1 .. 65535 (a 2-symbol table cannot hold 65536)
+  uint16_t cmpl;       // 2^16 - freq
+  uint32_t shift;
+  uint32_t pad;
+};
+
 struct vcm_cdf_tables {
   int32_t ntab = 0, stride = 0;
   std::vector<uint32_t> cdf;      // [ntab][stride]
   std::vector<int32_t> sizes, offsets;
   std::vector<uint8_t> lut;       // [ntab][256]: first symbol whose upper bound exceeds bucket<<8
+  std::vector<EncSym> enc;        // [ntab][stride]
+  std::vector<uint32_t> mode;     // [ntab][4]: most probable value, its start, its freq, 0
 };
 
 struct vcm_rans_enc {
-  std::vector<uint32_t> pending;  // start | range << 16 ; range == 0 marks a 4-bit bypass digit
+  // address of the symbol's EncSym (8-byte aligned, bit 0 clear) or (4-bit bypass digit << 1) | 1.
+  // The tables pushed from must stay alive until the flush (the models keep them for their lifetime).
+  std::vector<uint64_t> pending;
   std::vector<uint32_t> out;
 };
 
@@ -73,6 +93,8 @@ extern "C" vcm_cdf_tables* vcm_cdf_tables_new(const int32_t* cdf, const int32_t*
   t->sizes.assign(sizes, sizes + ntab);
   t->offsets.assign(offsets, offsets + ntab);
   t->lut.resize((size_t)ntab * 256);
+  t->enc.assign((size_t)ntab * stride, EncSym{});
+  t->mode.assign((size_t)ntab * 4, 0u);
   for (int32_t i = 0; i < ntab; ++i) {
     const int32_t sz = sizes[i];
     if (sz < 3 || sz > stride) {
@@ -88,6 +110,36 @@ extern "C" vcm_cdf_tables* vcm_cdf_tables_new(const int32_t* cdf, const int32_t*
       while (s + 1 < sz - 1 && row[s + 1] <= cum) ++s;
       t->lut[(size_t)i * 256 + b] = (uint8_t)s;
     }
+    uint32_t best = 0;
+    for (int32_t v = 0; v < sz - 1; ++v) {
+      const uint32_t start = row[v], freq = row[v + 1] - row[v];
+      if (row[v + 1] <= row[v] || freq > 65535u || row[v + 1] > (1u << kPrecision)) {
+        vcm_set_error("vcm_cdf_tables_new: table %d is not a strictly increasing 16-bit cdf", i);
+        delete t;
+        return nullptr;
+      }
+      EncSym& e = t->enc[(size_t)i * stride + v];
+      e.freq = (uint16_t)freq;
+      e.cmpl = (uint16_t)((1u << kPrecision) - freq);
+      if (freq == 1) {
+        e.rcp = ~0ull;
+        e.shift = 0;
+        e.bias = start + (1u << kPrecision) - 1;
+      } else {
+        uint32_t l = 1;
+        while ((1u << l) < freq) ++l;
+        e.rcp = (uint64_t)((((unsigned __int128)1 << (63 + l)) + freq - 1) / freq);
+        e.shift = l - 1;
+        e.bias = start;
+      }
+      if (v < sz - 2 && freq > best) {   // decoder fast path: most probable in-table value (never the escape)
+        best = freq;
+        uint32_t* m = &t->mode[(size_t)i * 4];
+        m[0] = (uint32_t)v;
+        m[1] = start;
+        m[2] = freq;
+      }
+    }
   }
   return t;
 }
@@ -99,9 +151,8 @@ extern "C" void vcm_rans_enc_reset(vcm_rans_enc* e) {
   if (e) e->pending.clear();
 }
 
-static inline void push_symbol(std::vector<uint32_t>& pend, const vcm_cdf_tables* t, int32_t ti,
+static inline void push_symbol(std::vector<uint64_t>& pend, const vcm_cdf_tables* t, int32_t ti,
                                int32_t symbol) {
-  const uint32_t* cdf = &t->cdf[(size_t)ti * t->stride];
   const int32_t max_value = t->sizes[ti] - 2;
   int32_t value = symbol - t->offsets[ti];
   uint32_t raw = 0;
@@ -112,18 +163,17 @@ static inline void push_symbol(std::vector<uint32_t>& pend, const vcm_cdf_tables
     raw = (uint32_t)(2 * (value - max_value));
     value = max_value;
   }
-  const uint32_t start = cdf[value], range = cdf[value + 1] - cdf[value];
-  pend.push_back(start | (range << 16));
+  pend.push_back((uint64_t)(uintptr_t)&t->enc[(size_t)ti * t->stride + value]);
   if (value == max_value) {
     int32_t nb = 0;
     while ((raw >> (nb * kBypassBits)) != 0) ++nb;
     int32_t v = nb;
     while (v >= kBypassMax) {
-      pend.push_back((uint32_t)kBypassMax);
+      pend.push_back(((uint64_t)kBypassMax << 1) | 1u);
       v -= kBypassMax;
     }
-    pend.push_back((uint32_t)v);
-    for (int32_t j = 0; j < nb; ++j) pend.push_back((raw >> (j * kBypassBits)) & kBypassMax);
+    pend.push_back(((uint64_t)v << 1) | 1u);
+    for (int32_t j = 0; j < nb; ++j) pend.push_back(((uint64_t)((raw >> (j * kBypassBits)) & kBypassMax) << 1) | 1u);
   }
 }
 
@@ -167,25 +217,26 @@ extern "C" int64_t vcm_rans_enc_flush(vcm_rans_enc* e, const uint8_t** bytes) {
   uint32_t* const end = e->out.data() + e->out.size();
   uint32_t* ptr = end;
   uint64_t x = kRansL;
-  const uint32_t* pend = e->pending.data();
+  const uint64_t* pend = e->pending.data();
   for (size_t i = n; i-- > 0;) {
-    const uint32_t s = pend[i];
-    const uint32_t range = s >> 16;
-    if (range) {
-      const uint32_t start = s & 0xffffu;
-      const uint64_t limit = ((kRansL >> kPrecision) << 32) * (uint64_t)range;
+    const uint64_t p = pend[i];
+    if (!(p & 1u)) {
+      const EncSym* s = reinterpret_cast<const EncSym*>((uintptr_t)p);
+      if (i >= 8) __builtin_prefetch(reinterpret_cast<const void*>((uintptr_t)(pend[i - 8] & ~(uint64_t)1)));
+      const uint64_t limit = (uint64_t)s->freq << (31 - kPrecision + 32);   // ((L >> 16) << 32) * freq
       if (x >= limit) {
         *--ptr = (uint32_t)x;
         x >>= 32;
       }
-      x = ((x / range) << kPrecision) + (x % range) + start;
+      const uint64_t q = (uint64_t)(((unsigned __int128)x * s->rcp) >> 64) >> s->shift;
+      x = x + s->bias + q * s->cmpl;
     } else {
-      const uint64_t limit = ((kRansL >> 16) << 32) * (uint64_t)(1u << (16 - kBypassBits));
+      const uint64_t limit = 1ull << (31 - kPrecision + 32 + 16 - kBypassBits);   // freq = 2^(16-4)
       if (x >= limit) {
         *--ptr = (uint32_t)x;
         x >>= 32;
       }
-      x = (x << kBypassBits) | (s & 0xffffu);
+      x = (x << kBypassBits) | (p >> 1);
     }
   }
   ptr -= 2;
@@ -228,6 +279,15 @@ struct DecCursor {
     const uint32_t* cdf = &t->cdf[(size_t)ti * t->stride];
     const int32_t max_value = t->sizes[ti] - 2;
     const uint32_t cum = (uint32_t)(x & 0xffffu);
+    {   // most probable value first: its record depends only on the table index, not on the state
+      const uint32_t* m = &t->mode[(size_t)ti * 4];
+      const uint32_t d = cum - m[1];
+      if (d < m[2]) {
+        x = (uint64_t)m[2] * (x >> kPrecision) + d;
+        if (x < kRansL) x = (x << 32) | next();
+        return (int32_t)m[0] + t->offsets[ti];
+      }
+    }
     int32_t s = t->lut[(size_t)ti * 256 + (cum >> 8)];
     while (cdf[s + 1] <= cum) ++s;
     const uint32_t start = cdf[s], freq = cdf[s + 1] - start;

@@ -141,6 +141,7 @@ class RansCoder:
         self.enc = L.vcm_rans_enc_new()
         self.dec = L.vcm_rans_dec_new()
         self._stream = None
+        self._live = []        # tables pushed from since the last flush: the encoder points into them
 
     def __del__(self):
         try:
@@ -151,11 +152,13 @@ class RansCoder:
 
     def reset_encoder(self):
         self.L.vcm_rans_enc_reset(self.enc)
+        self._live.clear()
 
     def encode_planes(self, sym, idx, tables):
         """sym int16 / idx uint8 host tensors of equal numel (GaussianEncoder.encode, :270-274)."""
         assert sym.dtype == torch.int16 and idx.dtype == torch.uint8 and sym.numel() == idx.numel()
         assert sym.device.type == "cpu" and sym.is_contiguous() and idx.is_contiguous()
+        self._live.append(tables)
         _lib.check(self.L.vcm_rans_enc_push(self.enc, sym.data_ptr(), idx.data_ptr(), sym.numel(), tables.h),
                    "vcm_rans_enc_push")
 
@@ -164,12 +167,14 @@ class RansCoder:
         assert sym.dtype == torch.int16 and sym.device.type == "cpu" and sym.is_contiguous()
         assert sym.dim() == 4 and sym.shape[0] == 1, "the bitstream path is batch 1 (entropy_models.py:186)"
         C, hw = sym.shape[1], sym.shape[2] * sym.shape[3]
+        self._live.append(tables)
         _lib.check(self.L.vcm_rans_enc_push_channels(self.enc, sym.data_ptr(), C, hw, tables.h),
                    "vcm_rans_enc_push_channels")
 
     def flush_encoder(self):
         p = ctypes.c_void_p()
         n = self.L.vcm_rans_enc_flush(self.enc, ctypes.byref(p))
+        self._live.clear()
         if n < 0:
             raise _lib.VcmError("vcm_rans_enc_flush: " + self.L.vcm_last_error().decode())
         return ctypes.string_at(p, n)
