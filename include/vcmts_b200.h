@@ -107,6 +107,21 @@ int vcm_u8hwc_to_frame(const uint8_t* src, float* dst, int32_t N, int32_t H, int
                        int32_t Wp, void* stream);
 int vcm_frame_to_u8hwc(const float* src, uint8_t* dst, int32_t N, int32_t H, int32_t W, int32_t Hs,
                        int32_t Ws, void* stream);
+/* ---- enhancement layer: uint8 HWC frames [N][H][W][C] on the device ----
+ * boxes: int32 [total][4] = (x1, y1, x2, y2), already normalised to 0 <= x1 <= x2 <= W, 0 <= y1 <= y2 <= H;
+ * box_start: int32 [N + 1], frame n owns boxes [box_start[n], box_start[n+1]) (<= 256 per frame, in the
+ * order the reference assigns them: later boxes overwrite earlier ones); max_boxes: largest per-frame count.
+ * vcm_enh_residual = compute_residuals' per-frame statements (video_coder.py:415-447):
+ *   out = inside any box ? clip(src - enc + 128, 0, 255) : 0
+ * vcm_enh_fuse = fuse_layers' per-frame statements (video_coder.py:570-600) with create_gradient_mask
+ *   (:521-530): out = clip(base + mask * (enh - 128), 0, 255), mask = 0 outside the boxes and inside box b
+ *   ring[ring_start[b] + min(d, len_b - 1)], d = distance to the box border, len_b = ring_start[b+1] -
+ *   ring_start[b]; ring holds float32(1 - linspace(0.9, 0, border)) per box ({1.0} for border 0).        */
+int vcm_enh_residual(const uint8_t* src, const uint8_t* enc, uint8_t* out, int32_t N, int32_t H, int32_t W,
+                     int32_t C, const int32_t* boxes, const int32_t* box_start, int32_t max_boxes, void* stream);
+int vcm_enh_fuse(const uint8_t* base, const uint8_t* enh, uint8_t* out, int32_t N, int32_t H, int32_t W, int32_t C,
+                 const int32_t* boxes, const int32_t* box_start, const int32_t* ring_start, const float* ring,
+                 int32_t max_boxes, void* stream);
 /* NHWC view -> NCHW fp32, optional clamp to [lo,hi] (video_model.py:413 `recon.clamp(0,1)`)  */
 int vcm_nhwc_to_nchw(const void* src, float* dst, int32_t N, int32_t C, int32_t H, int32_t W,
                      int32_t src_cstride, int32_t dtype, int32_t do_clamp, float lo, float hi,

@@ -51,6 +51,8 @@ _PROTOS = {
     "vcm_nchw_to_nhwc": (c_int, [_P, _P, c_int32, c_int32, c_int32, c_int32, c_int32, c_int32, _P]),
     "vcm_u8hwc_to_frame": (c_int, [_P, _P, c_int32, c_int32, c_int32, c_int32, c_int32, _P]),
     "vcm_frame_to_u8hwc": (c_int, [_P, _P, c_int32, c_int32, c_int32, c_int32, c_int32, _P]),
+    "vcm_enh_residual": (c_int, [_P, _P, _P, c_int32, c_int32, c_int32, c_int32, _P, _P, c_int32, _P]),
+    "vcm_enh_fuse": (c_int, [_P, _P, _P, c_int32, c_int32, c_int32, c_int32, _P, _P, _P, _P, c_int32, _P]),
     "vcm_nhwc_to_nchw": (c_int, [_P, _P, c_int32, c_int32, c_int32, c_int32, c_int32, c_int32,
                                  c_int32, c_float, c_float, _P]),
     "vcm_copy_channels": (c_int, [_P, _P, c_int64, c_int32, c_int32, c_int32, c_int32, c_int32, _P]),
