@@ -141,6 +141,9 @@ def code_gop(dmc, intra, frames_src, gop, q, host_out=None, pinned_in=False, dev
     return bits, rec
 
 
+PEAK_TC, PEAK_HBM = 1400.0, 6500.0      # TFLOP/s, GB/s; replaced by MEASURED_PEAKS.json in main()
+
+
 def conv_roofline(dmc, intra, x, dpb, q):
     """Instrumented pass: CUDA events around every conv launch of one P-frame encode+decode, on the
     launching stream.  Returns achieved TFLOP/s of the tcgen05 engine (algorithmic FLOPs / time)."""
@@ -180,7 +183,14 @@ def conv_roofline(dmc, intra, x, dpb, q):
         a[0] += e0.elapsed_time(e1)
         a[1] += f
         a[2] += 1
-    return dict(tc_s=tc_t, tc_flop=tc_f, all_s=all_t, all_flop=all_f, n=len(recs),
+    # SURVEY 8(d) "which roofline": per layer max(flops / tensor peak, bytes / HBM peak), activations read once
+    # and written once in bf16 (weights and residual operands not counted)
+    roof_s = 0.0
+    for _, _, f, _, (k, stride, cin, cout, hh, ww) in recs:
+        ho, wo = (hh + stride - 1) // stride, (ww + stride - 1) // stride
+        nbytes = 2.0 * (hh * ww * cin + ho * wo * cout)
+        roof_s += max(f / (PEAK_TC * 1e12), nbytes / (PEAK_HBM * 1e9))
+    return dict(tc_s=tc_t, tc_flop=tc_f, all_s=all_t, all_flop=all_f, n=len(recs), per_layer_roof_s=roof_s,
                 n_tc=sum(1 for r in recs if r[3]), by_shape=by_shape)
 
 
@@ -394,12 +404,15 @@ def main():
         x1, x0 = seq_dev[1:2], seq_dev[0:1]
         r0, _ = intra.encode_decode_bytes(x0, q, H, W)
         dpb = {"ref_frame": r0["x_hat"], "ref_feature": None, "ref_y": None, "ref_mv_y": None}
-        rf = conv_roofline(dmc, intra, x1, dpb, q)
         peaks = {}
         try:
             peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
         except Exception:
             pass
+        global PEAK_TC, PEAK_HBM
+        PEAK_TC = peaks.get("bf16_tflops_sustained", PEAK_TC)
+        PEAK_HBM = peaks.get("hbm_gbs", PEAK_HBM)
+        rf = conv_roofline(dmc, intra, x1, dpb, q)
         peak = peaks.get("bf16_tflops_sustained", 1400.0)
         use_tc = rf["tc_s"] > 0
         ach = (rf["tc_flop"] / rf["tc_s"] if use_tc else rf["all_flop"] / max(rf["all_s"], 1e-9)) / 1e12
@@ -408,6 +421,11 @@ def main():
                 "peak_source": "MEASURED_PEAKS.json bf16_tflops_sustained" if peaks else "fallback 1400 (sustained)",
                 "traffic": None,
                 "launches_timed": rf["n_tc"] if use_tc else rf["n"],
+                "per_layer_bound": {"what": "sum over the conv launches of one P-frame of max(flops/tensor peak, "
+                                            "activation bytes/HBM peak) / measured conv time (SURVEY 8(d))",
+                                    "roofline_ms": rf["per_layer_roof_s"] * 1e3, "measured_ms": rf["all_s"] * 1e3,
+                                    "frac": rf["per_layer_roof_s"] / max(rf["all_s"], 1e-9),
+                                    "hbm_peak_gbs": PEAK_HBM},
                 "conv_share_of_p_frame": {"tc_ms": rf["tc_s"] * 1e3, "all_conv_ms": rf["all_s"] * 1e3,
                                           "all_conv_tflops": rf["all_flop"] / max(rf["all_s"], 1e-9) / 1e12}}
         top = sorted(rf["by_shape"].items(), key=lambda kv: -kv[1][0])
