@@ -375,3 +375,38 @@ def test_cuda_graph_mode_equals_eager_coding(precision):
         for t in range(5):
             assert torch.equal(got[t], want_rec[t]), (gop, t)
     assert enc[0]._rt.B.graph_replays > 0 and dec[0]._rt.B.graph_replays > 0
+
+
+def test_cuda_graphs_follow_a_weight_reload():
+    """Captured graphs bake in the addresses of the packed weights: load_state_dict must drop them,
+    and coding with the new weights must again equal an eager model with those weights."""
+    from oracle import fixture
+    dev = "cuda:0"
+    fr = fixture.fixture_frames(128, 192, 4, seed=13).to(dev)
+    ref_frame = fr[0:1].clone()
+
+    def chain(dmc, n=3):
+        out = []
+        dpb = {"ref_frame": ref_frame, "ref_feature": None, "ref_y": None, "ref_mv_y": None}
+        for t in range(1, 4):
+            r, blob = dmc.encode_decode_bytes(fr[t:t + 1], dpb, 128, 192, 1.0, 1.0)
+            dpb = r["dpb"]
+            out.append((blob, dpb["ref_frame"].clone()))
+        return out
+
+    dmc, _ = _models("bf16")
+    dmc.set_cuda_graphs(True)
+    for _ in range(3):
+        first = chain(dmc)
+    assert dmc._rt.B.graph_replays > 0
+    sd = {k: (v * 0.9 if k.endswith(".weight") and v.dim() == 4 else v) for k, v in dmc.state_dict().items()}
+    dmc.load_state_dict(sd)
+    assert not dmc._rt.programs.progs
+    eager, _ = _models("bf16")
+    eager.load_state_dict(sd)
+    want = chain(eager)
+    assert want[0][0] != first[0][0]
+    for _ in range(3):
+        got = chain(dmc)
+        for (b0, r0), (b1, r1) in zip(want, got):
+            assert b0 == b1 and torch.equal(r0, r1)

@@ -133,6 +133,9 @@ class _EagerPrograms:
     def __init__(self, device):
         self.device, self.keys = device, []
 
+    def invalidate(self):
+        self.keys.clear()
+
     def run(self, key, make_gen, service):
         from vcm_ts_b200.graphs import drive_eager
         self.keys.append(key)

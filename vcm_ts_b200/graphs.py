@@ -78,12 +78,24 @@ class ProgramCache:
         self.seen = set()
         self.progs = {}
 
+    MAX_PROGRAMS = 32      # distinct (shape, q, reference-state) keys kept; beyond that start over
+
+    def invalidate(self):
+        """Drop every captured program (their graphs bake in the addresses of packed weights, q
+        vectors and static buffers): called when the model's parameters are reloaded."""
+        self.progs.clear()
+        self.seen.clear()
+        self.pool = None       # the pool dies with its last graph: captures after this get a fresh one
+
     def run(self, key, make_gen, service):
         prog = self.progs.get(key)
         if prog is None:
             if key not in self.seen:
                 self.seen.add(key)
                 return drive_eager(make_gen(), service, self.B.device)
+            if len(self.progs) >= self.MAX_PROGRAMS:
+                self.progs.clear()
+                self.pool = None
             prog = self._capture(make_gen)
             self.progs[key] = prog
         return prog.replay(service)

@@ -112,14 +112,28 @@ class CompressionModel(nn.Module):
             self._precision, self._rt = precision, None
         return self
 
+    def load_state_dict(self, *args, **kwargs):
+        out = super().load_state_dict(*args, **kwargs)
+        self.reset_cuda_graphs()        # captured graphs point at the previously packed weights
+        return out
+
     def set_cuda_graphs(self, enabled=True):
         """Opt-in: capture the per-frame launch sequences of compress / decompress into CUDA graphs
         (graphs.py).  In this mode the returned dpb is a set of STATIC buffers owned by the model
         (ref_frame an NCHW fp32 tensor as usual, ref_feature / ref_y / ref_mv_y internal NHWC views):
         the next call overwrites them in place, so use them (or copy them) before coding the next
-        frame.  Symbols, bitstreams and reconstructions are identical to the eager mode."""
+        frame.  Symbols, bitstreams and reconstructions are identical to the eager mode.  One model
+        instance holds one chain per side and must be driven from one thread / stream at a time;
+        `load_state_dict` drops the captured graphs (in-place edits of parameters behind the model's
+        back are not detected while replaying -- call `reset_cuda_graphs()` after them)."""
         self._graphs = bool(enabled)
         return self
+
+    def reset_cuda_graphs(self):
+        """Drop the captured graphs; the next frames run eagerly once and are captured again."""
+        if self._rt is not None:
+            self._rt.programs.invalidate()
+            self._rt.qcache.clear()
 
     @property
     def device(self):
