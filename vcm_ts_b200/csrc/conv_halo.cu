@@ -68,10 +68,7 @@ __device__ __forceinline__ void mma_role(const HaloGeom& G, const HaloBars& B, u
   constexpr uint32_t AHALF16 = HTH * ALINE16;        // second 128-pixel half (MH == 2)
   int as = 0, bs = 0, acc = 0;   // bs / bphase live in the elected lane only (always the same lane)
   uint32_t aphase = 0, bphase = 0, acc_phase = 0;
-  if (RESIDENT) {
-    mbar_wait(&B.bfull[0], 0);
-    tc_fence_after();
-  }
+  bool first = true;   // resident weights: wait for each tap's slabs while the first tile is issued
   const uint64_t bdesc0 = make_smem_desc(b_smem, 8u * ROWB, LAYOUT);
   const uint32_t bslot16 = (uint32_t)G.b_slot_bytes >> 4;
   const uint32_t btap16 = bslot16 * (uint32_t)G.nchunks;   // resident: slab index = tap * nchunks + ch
@@ -94,6 +91,10 @@ __device__ __forceinline__ void mma_role(const HaloGeom& G, const HaloBars& B, u
             const int tap = ky * K + kx;
             uint64_t bdesc;
             if (RESIDENT) {
+              if (first) {
+                mbar_wait(&B.bfull[tap < H_MAX_B - 1 ? tap : H_MAX_B - 1], 0);
+                tc_fence_after();
+              }
               bdesc = bch + (uint64_t)((uint32_t)tap * btap16);
             } else {
               mbar_wait(&B.bfull[bs], bphase);
@@ -120,6 +121,7 @@ __device__ __forceinline__ void mma_role(const HaloGeom& G, const HaloBars& B, u
         umma_commit(&B.aempty[as]);
         if (ch == G.nchunks - 1) umma_commit(&B.tfull[acc]);
       }
+      first = false;
       __syncwarp();
       if (++as == G.a_stages) { as = 0; aphase ^= 1u; }
     }
@@ -194,10 +196,18 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     // ============================ weight producer ==============================================
     if (lane == 0) {
       if (G.resident) {
-        const int slabs = G.ntaps * G.nchunks;
-        mbar_expect_tx(&bfull[0], (uint32_t)(slabs * G.b_bytes));
-        for (int s = 0; s < slabs; ++s)
-          tma_load_2d(smem_u32(smem + G.b_base + (size_t)s * G.b_slot_bytes), &tmB, &bfull[0], 0, s * G.cout_p);
+        // one barrier per tap (the taps past H_MAX_B - 1 share the last one), in the order the MMA role
+        // consumes them: the first tile starts after 1/ntaps of the weights has landed, not all of them
+        for (int tap = 0; tap < G.ntaps; ++tap) {
+          const int bi = tap < H_MAX_B - 1 ? tap : H_MAX_B - 1;
+          if (tap <= H_MAX_B - 1)
+            mbar_expect_tx(&bfull[bi], (uint32_t)((tap < H_MAX_B - 1 ? 1 : G.ntaps - (H_MAX_B - 1)) * G.nchunks *
+                                                  G.b_bytes));
+          for (int ch = 0; ch < G.nchunks; ++ch) {
+            const int s = tap * G.nchunks + ch;
+            tma_load_2d(smem_u32(smem + G.b_base + (size_t)s * G.b_slot_bytes), &tmB, &bfull[bi], 0, s * G.cout_p);
+          }
+        }
       } else {
         int stage = 0;
         uint32_t phase = 0;
