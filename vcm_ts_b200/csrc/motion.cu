@@ -180,19 +180,21 @@ __global__ void flow_warp_kernel(const T* __restrict__ feat, const float* __rest
 
 // bf16, 8 channels (16 bytes) per thread: same per-channel arithmetic, half the instructions and
 // twice the bytes in flight per thread of the 4-channel variant
-__global__ void flow_warp8_bf16_kernel(const __nv_bfloat16* __restrict__ feat, const float* __restrict__ flow,
-                                       __nv_bfloat16* __restrict__ out, int N, int H, int W, int C, int feat_cs,
-                                       int flow_cs, int out_cs) {
+// A block owns an 8 x (256 / G / 8) pixel patch (G = C / 8 threads per pixel), not a run of a row: the four
+// taps of neighbouring output pixels overlap in both directions, so most of the 4x gather amplification is
+// served by L1 instead of L2.  grid = (tiles_x, tiles_y, N).
+__global__ void __launch_bounds__(256) flow_warp8_bf16_kernel(const __nv_bfloat16* __restrict__ feat,
+                                                              const float* __restrict__ flow,
+                                                              __nv_bfloat16* __restrict__ out, int N, int H, int W,
+                                                              int C, int feat_cs, int flow_cs, int out_cs) {
   const int G = C / 8;
-  const int64_t total = (int64_t)N * H * W * G;
-  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total;
-       i += (int64_t)gridDim.x * blockDim.x) {
-    const int g = (int)(i % G);
-    const int64_t p = i / G;
-    const int ox = (int)(p % W);
-    const int64_t q = p / W;
-    const int oy = (int)(q % H);
-    const int n = (int)(q / H);
+  const int th = 256 / G / 8;
+  {
+    const int g = threadIdx.x % G, pix = threadIdx.x / G;
+    const int ox = blockIdx.x * 8 + (pix & 7), oy = blockIdx.y * th + (pix >> 3);
+    const int n = blockIdx.z;
+    if (ox >= W || oy >= H) return;
+    const int64_t p = ((int64_t)n * H + oy) * W + ox;
     const float2 uv = __ldg(reinterpret_cast<const float2*>(flow + p * flow_cs));
     const WarpTaps t = warp_taps(uv.x, uv.y, ox, oy, W, H);
     const __nv_bfloat16* b = feat + (int64_t)n * H * W * feat_cs + g * 8;
@@ -257,9 +259,10 @@ extern "C" int vcm_flow_warp(const void* feat, const float* flow, void* out, int
                    ((uintptr_t)feat % (4 * esz) == 0) && ((uintptr_t)out % (4 * esz) == 0);
   const int64_t total = (int64_t)N * H * W * (vec ? C / 4 : C);
   cudaStream_t s = (cudaStream_t)stream;
-  if (dtype == VCM_BF16 && C % 8 == 0 && feat_cstride % 8 == 0 && out_cstride % 8 == 0 && flow_cstride % 2 == 0 &&
+  if (dtype == VCM_BF16 && C % 8 == 0 && C <= 256 && 256 % (C / 8) == 0 && N <= 65535 && feat_cstride % 8 == 0 && out_cstride % 8 == 0 && flow_cstride % 2 == 0 &&
       (uintptr_t)feat % 16 == 0 && (uintptr_t)out % 16 == 0 && (uintptr_t)flow % 8 == 0) {
-    flow_warp8_bf16_kernel<<<ew_grid((int64_t)N * H * W * (C / 8)), 256, 0, s>>>(
+    const int th = 256 / (C / 8) / 8;
+    flow_warp8_bf16_kernel<<<dim3((W + 7) / 8, (H + th - 1) / th, N), 256, 0, s>>>(
         (const __nv_bfloat16*)feat, flow, (__nv_bfloat16*)out, N, H, W, C, feat_cstride, flow_cstride, out_cstride);
     VCM_CHECK_LAUNCH();
     return 0;
