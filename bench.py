@@ -364,8 +364,9 @@ def main():
     def step_e2e():
         run_all(one_e2e)
 
-    # warm-up (>= 3 coded frames each through both models; W steps of a short GOP)
-    for _ in range(max(a.warmup, 1)):
+    # warm-up: W steps of a short GOP (I + 2 P) through both models, at least 3 so that every per-frame
+    # program has had its eager pass and its capture pass (vcm_ts_b200/graphs.py) before anything is timed
+    for _ in range(max(a.warmup, 3)):
         run_all(lambda w: one_resident(w, min(gop, 3)))
     backends = [w[m]._rt.B for w in workers for m in ("dmc", "intra")]
     clocks = ClockSampler(local)
