@@ -82,8 +82,27 @@ __global__ void __launch_bounds__(256) enh_kernel(const uint8_t* __restrict__ a,
     const uint4* a4 = reinterpret_cast<const uint4*>(a + (int64_t)n * hw * 3);
     const uint4* b4 = reinterpret_cast<const uint4*>(b + (int64_t)n * hw * 3);
     uint4* o4 = reinterpret_cast<uint4*>(out + (int64_t)n * hw * 3);
-    for (int w = blockIdx.x * blockDim.x + threadIdx.x; w < words; w += (int)step) {
-      const int y = (16 * w) / row_bytes, r = 16 * w - y * row_bytes;
+    // rows any box reaches: everything outside is decided without scanning the boxes
+    int ylo = H, yhi = 0;
+    for (int i = 0; i < nb; ++i) {
+      if (sb.box[i].z > sb.box[i].x) {
+        ylo = min(ylo, sb.box[i].y);
+        yhi = max(yhi, sb.box[i].w);
+      }
+    }
+    // (row, byte in row) of this thread's word, advanced incrementally (no division per word)
+    const int w_first = blockIdx.x * blockDim.x + threadIdx.x;
+    const int dy = (16 * (int)step) / row_bytes, dr = 16 * (int)step - dy * row_bytes;
+    int y = (16 * w_first) / row_bytes, r = 16 * w_first - y * row_bytes;
+    for (int w = w_first; w < words; w += (int)step, y += dy, r += dr) {
+      if (r >= row_bytes) {
+        r -= row_bytes;
+        ++y;
+      }
+      if (y < ylo || y >= yhi) {
+        o4[w] = FUSE ? __ldg(a4 + w) : make_uint4(0u, 0u, 0u, 0u);
+        continue;
+      }
       const int x0 = r / 3, x1 = (r + 15) / 3;
       // untouched by any box (the common case): residual 0 / base layer copied, nothing else read;
       // entirely inside boxes with mask 1: packed-byte integer arithmetic; box edges and gradient
