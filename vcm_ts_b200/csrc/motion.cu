@@ -180,7 +180,7 @@ __global__ void flow_warp_kernel(const T* __restrict__ feat, const float* __rest
 
 // bf16, 8 channels (16 bytes) per thread: same per-channel arithmetic, half the instructions and
 // twice the bytes in flight per thread of the 4-channel variant
-// A block owns an 8 x (256 / G / 8) pixel patch (G = C / 8 threads per pixel), not a run of a row: the four
+// A block owns an 8 x 2*(256 / G / 8) pixel patch (G = C / 8 threads per pixel), not a run of a row: the four
 // taps of neighbouring output pixels overlap in both directions, so most of the 4x gather amplification is
 // served by L1 instead of L2.  grid = (tiles_x, tiles_y, N).
 __global__ void __launch_bounds__(256) flow_warp8_bf16_kernel(const __nv_bfloat16* __restrict__ feat,
@@ -189,32 +189,47 @@ __global__ void __launch_bounds__(256) flow_warp8_bf16_kernel(const __nv_bfloat1
                                                               int C, int feat_cs, int flow_cs, int out_cs) {
   const int G = C / 8;
   const int th = 256 / G / 8;
-  {
-    const int g = threadIdx.x % G, pix = threadIdx.x / G;
-    const int ox = blockIdx.x * 8 + (pix & 7), oy = blockIdx.y * th + (pix >> 3);
-    const int n = blockIdx.z;
-    if (ox >= W || oy >= H) return;
-    const int64_t p = ((int64_t)n * H + oy) * W + ox;
-    const float2 uv = __ldg(reinterpret_cast<const float2*>(flow + p * flow_cs));
-    const WarpTaps t = warp_taps(uv.x, uv.y, ox, oy, W, H);
-    const __nv_bfloat16* b = feat + (int64_t)n * H * W * feat_cs + g * 8;
-    const uint4 v00 = __ldg(reinterpret_cast<const uint4*>(b + ((int64_t)t.y0 * W + t.x0) * feat_cs));
-    const uint4 v01 = __ldg(reinterpret_cast<const uint4*>(b + ((int64_t)t.y0 * W + t.x1) * feat_cs));
-    const uint4 v10 = __ldg(reinterpret_cast<const uint4*>(b + ((int64_t)t.y1 * W + t.x0) * feat_cs));
-    const uint4 v11 = __ldg(reinterpret_cast<const uint4*>(b + ((int64_t)t.y1 * W + t.x1) * feat_cs));
-    const __nv_bfloat162* h00 = reinterpret_cast<const __nv_bfloat162*>(&v00);
-    const __nv_bfloat162* h01 = reinterpret_cast<const __nv_bfloat162*>(&v01);
-    const __nv_bfloat162* h10 = reinterpret_cast<const __nv_bfloat162*>(&v10);
-    const __nv_bfloat162* h11 = reinterpret_cast<const __nv_bfloat162*>(&v11);
+  constexpr int PP = 2;   // pixels per thread (rows oy and oy + th): both flow loads, then all eight tap loads
+  const int g = threadIdx.x % G, pix = threadIdx.x / G;
+  const int ox = blockIdx.x * 8 + (pix & 7);
+  const int n = blockIdx.z;
+  if (ox >= W) return;
+  const __nv_bfloat16* b = feat + (int64_t)n * H * W * feat_cs + g * 8;
+  int oy[PP];
+  int64_t p[PP];
+  float2 uv[PP];
+#pragma unroll
+  for (int j = 0; j < PP; ++j) {
+    oy[j] = blockIdx.y * (PP * th) + j * th + (pix >> 3);
+    p[j] = ((int64_t)n * H + min(oy[j], H - 1)) * W + ox;
+    uv[j] = __ldg(reinterpret_cast<const float2*>(flow + p[j] * flow_cs));
+  }
+  WarpTaps t[PP];
+  uint4 v[PP][4];
+#pragma unroll
+  for (int j = 0; j < PP; ++j) {
+    t[j] = warp_taps(uv[j].x, uv[j].y, ox, min(oy[j], H - 1), W, H);
+    v[j][0] = __ldg(reinterpret_cast<const uint4*>(b + ((int64_t)t[j].y0 * W + t[j].x0) * feat_cs));
+    v[j][1] = __ldg(reinterpret_cast<const uint4*>(b + ((int64_t)t[j].y0 * W + t[j].x1) * feat_cs));
+    v[j][2] = __ldg(reinterpret_cast<const uint4*>(b + ((int64_t)t[j].y1 * W + t[j].x0) * feat_cs));
+    v[j][3] = __ldg(reinterpret_cast<const uint4*>(b + ((int64_t)t[j].y1 * W + t[j].x1) * feat_cs));
+  }
+#pragma unroll
+  for (int j = 0; j < PP; ++j) {
+    if (oy[j] >= H) continue;
+    const __nv_bfloat162* h00 = reinterpret_cast<const __nv_bfloat162*>(&v[j][0]);
+    const __nv_bfloat162* h01 = reinterpret_cast<const __nv_bfloat162*>(&v[j][1]);
+    const __nv_bfloat162* h10 = reinterpret_cast<const __nv_bfloat162*>(&v[j][2]);
+    const __nv_bfloat162* h11 = reinterpret_cast<const __nv_bfloat162*>(&v[j][3]);
     uint4 r;
     __nv_bfloat162* hr = reinterpret_cast<__nv_bfloat162*>(&r);
 #pragma unroll
     for (int k = 0; k < 4; ++k) {
       const float2 a = __bfloat1622float2(h00[k]), bb = __bfloat1622float2(h01[k]);
       const float2 cc = __bfloat1622float2(h10[k]), dd = __bfloat1622float2(h11[k]);
-      hr[k] = __floats2bfloat162_rn(warp_mix(t, a.x, bb.x, cc.x, dd.x), warp_mix(t, a.y, bb.y, cc.y, dd.y));
+      hr[k] = __floats2bfloat162_rn(warp_mix(t[j], a.x, bb.x, cc.x, dd.x), warp_mix(t[j], a.y, bb.y, cc.y, dd.y));
     }
-    *reinterpret_cast<uint4*>(out + p * out_cs + g * 8) = r;
+    *reinterpret_cast<uint4*>(out + p[j] * out_cs + g * 8) = r;
   }
 }
 
@@ -262,7 +277,7 @@ extern "C" int vcm_flow_warp(const void* feat, const float* flow, void* out, int
   if (dtype == VCM_BF16 && C % 8 == 0 && C <= 256 && 256 % (C / 8) == 0 && N <= 65535 && feat_cstride % 8 == 0 && out_cstride % 8 == 0 && flow_cstride % 2 == 0 &&
       (uintptr_t)feat % 16 == 0 && (uintptr_t)out % 16 == 0 && (uintptr_t)flow % 8 == 0) {
     const int th = 256 / (C / 8) / 8;
-    flow_warp8_bf16_kernel<<<dim3((W + 7) / 8, (H + th - 1) / th, N), 256, 0, s>>>(
+    flow_warp8_bf16_kernel<<<dim3((W + 7) / 8, (H + 2 * th - 1) / (2 * th), N), 256, 0, s>>>(
         (const __nv_bfloat16*)feat, flow, (__nv_bfloat16*)out, N, H, W, C, feat_cstride, flow_cstride, out_cstride);
     VCM_CHECK_LAUNCH();
     return 0;
