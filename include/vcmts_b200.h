@@ -37,6 +37,13 @@ extern "C" {
 #define VCM_CONV_OUT2 64          /* also store leaky_relu(out, out2_slope) to y2: the activated
                                      twin a following ResBlock's first conv reads, so that the
                                      tensor-core engine never has to modify TMA-loaded tiles     */
+#define VCM_CONV_SPLIT3 128       /* parity mode of the tensor-core engine: x holds THREE bf16 planes
+                                     x0 | x1 | x2 with x0 + x1 + x2 == the fp32 activation exactly
+                                     (vcm_split_bf16x3), plane p at channel offset p*in_pstride, and
+                                     w_umma holds the three bf16 parts of the fp32 weights
+                                     (vcm_pack_conv_weight_umma_split3).  The engine issues the six
+                                     products x_i*w_j with i + j <= 2 (smallest first) into the fp32
+                                     TMEM accumulator: fp32-class accuracy on tcgen05.               */
 
 typedef struct {
   int32_t N, H, W;        /* input batch / height / width                                   */
@@ -48,6 +55,7 @@ typedef struct {
   int32_t in_dtype;       /* VCM_F32 | VCM_BF16 : storage of x                               */
   int32_t out_dtype;      /* storage of y, res and res2 (mixed in/out serves the fp32<->bf16
                              boundaries: flow fields and frames stay fp32)                    */
+  int32_t in_pstride;     /* VCM_CONV_SPLIT3: channels between consecutive bf16 planes of x   */
 } vcm_conv_desc;
 
 const char* vcm_last_error(void);
@@ -80,21 +88,18 @@ int vcm_pack_conv_weight_umma(const float* w_oihw, void* w_umma, int32_t Cout, i
 int vcm_conv2d_tc_fwd(const vcm_conv_desc* d, const void* x, const void* w_umma,
                       const float* bias, const void* res, const float* res_scale,
                       const void* res2, void* y, void* y2, void* stream);
-/* probe of the UMMA shared-memory descriptor semantics used by the halo-tile variant: runs
- * one 128x64x64 MMA whose A rows start `start_row` rows into a 128B-swizzled buffer with the
- * given stride between 8-row groups; out[128*64] fp32 = the A rows the tensor core read.     */
-int vcm_umma_probe(int32_t start_row, int32_t sbo_bytes, int32_t use_base_offset, float* out,
-                   void* stream);
-/* issue-rate probe: `iters` back-to-back 128xNx16 bf16 MMAs; out[0] = SM cycles, out[1] = iters */
-int vcm_umma_rate(int32_t N, int32_t iters, long long* out, void* stream);
-/* same, with the A operand starting `start_row` 128-byte rows into the buffer and 8-row groups sbo_bytes apart */
-int vcm_umma_rate2(int32_t N, int32_t iters, int32_t start_row, int32_t sbo_bytes, long long* out,
-                   void* stream);
-/* TMA box-shape throughput probe: all SMs stream {64 ch, bw, bh} boxes of an NHWC bf16 [H][W][64] image
- * through a `stages`-deep ring (each box as nsplit TMA ops); out[0] = cycles of CTA 0, out[1] = its boxes */
-int vcm_tma_probe(const void* img, int32_t H, int32_t W, int32_t bw, int32_t bh, int32_t stages,
-                  int32_t nsplit, long long* out, void* stream);
-
+/* parity mode (VCM_CONV_SPLIT3).  The reference computes every nn.Conv2d in fp32
+ * (video_model.py:17-224 has no autocast); its quantised symbols (common_model.py:91-102) flip
+ * under plain bf16 operands.  Splitting both operands into three bf16 terms keeps 24 significand
+ * bits: src fp32 view [npix][C] (cstride src_cstride), optional leaky_relu(pre_slope) first, ->
+ * dst bf16 planes p = 0..2 at dst + p*dst_pstride, each [npix][Cp] with cstride dst_cstride,
+ * channels C..Cp-1 zero.  x0 = bf16(x), x1 = bf16(x - x0), x2 = bf16(x - x0 - x1).
+ * Weights: 3 * vcm_conv2d_tc_weight_bytes bytes, layout [part][tap][chunk][Cout_p][CHUNK].      */
+int vcm_split_bf16x3(const float* src, void* dst, int64_t npix, int32_t C, int32_t Cp,
+                     int32_t src_cstride, int32_t dst_cstride, int32_t dst_pstride,
+                     int32_t pre_act, float pre_slope, void* stream);
+int vcm_pack_conv_weight_umma_split3(const float* w_oihw, void* w_umma, int32_t Cout, int32_t Cin,
+                                     int32_t K, int32_t Cin_p, const int32_t* in_map, void* stream);
 /* ---- layout / elementwise glue ------------------------------------------------------- */
 /* NCHW fp32 -> NHWC view (dtype) ; callers' tensors are NCHW fp32 (video_coder.py:99-117)  */
 int vcm_nchw_to_nhwc(const float* src, void* dst, int32_t N, int32_t C, int32_t H, int32_t W,

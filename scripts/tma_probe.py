@@ -1,8 +1,8 @@
 import os, sys, json
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
-from vcm_ts_b200 import _lib
-L = _lib.lib()
+from vcm_ts_b200 import _probe
+L = _probe.lib()
 H, W = 1088, 1920
 img = torch.randn((H, W, 64), device="cuda").to(torch.bfloat16)
 out = torch.zeros(2, dtype=torch.int64, device="cuda")
@@ -14,7 +14,7 @@ for bw, bh in ((8, 16), (10, 18), (16, 8), (18, 10), (32, 4), (34, 6), (64, 2), 
             continue
         for _ in range(2):
             rc = L.vcm_tma_probe(img.data_ptr(), H, W, bw, bh, stages, nsplit, out.data_ptr(), None)
-            assert rc == 0, _lib.last_error() if hasattr(_lib, "last_error") else rc
+            assert rc == 0, rc
             torch.cuda.synchronize()
         cyc, n = out[0].item(), out[1].item()
         r = dict(bw=bw, bh=bh, stages=stages, nsplit=nsplit, cycles_per_box=cyc / n, bytes_per_cycle_sm=bw * bh * 128 * n / cyc,

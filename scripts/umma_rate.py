@@ -1,8 +1,8 @@
 import os, sys, json
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
-from vcm_ts_b200 import _lib
-L = _lib.lib()
+from vcm_ts_b200 import _probe
+L = _probe.lib()
 out = torch.zeros(2, dtype=torch.int64, device="cuda")
 res = {}
 for N in (16, 32, 64, 128, 256):

@@ -1,15 +1,25 @@
 """`-m gpu` end-to-end parity: the drop-in DMC / IntraNoAR on a B200 against the golden vectors
 generated from the real reference (tests/golden, oracle/gen_golden.py) and against the oracle.
 
-fp32 (exact) mode
+Three numerics modes of the same graph: "fp32" (exact mode, fp32 FMA convs on CUDA cores), "parity"
+(the tcgen05 tensor-core engine on split-bf16 operands: three bf16 planes per activation, three parts per
+weight, six MMAs per product, fp32 accumulate) and "bf16" (plain bf16 tensor-core mode, what bench.py's
+headline measures).  north_star's bounds: symbols / bitstreams bit-exact, bpp within 0.1 %, PSNR within
+0.01 dB.
+
+fp32 and parity modes
   * tiny_64x128: free-running I + 2 P chain -- symbols, rANS streams and `.bin` containers BIT-EXACT.
   * cfg1_240x416 (BASELINE config 1 size): every frame is teacher-forced with the oracle's dpb, so a
     last-ulp difference between GPU FMA order and oneDNN cannot cascade.  A quantiser input that
     lands within float noise of a rounding boundary may flip by one step: the test bounds the flip
     rate (<= 2e-4 of the symbols, each by +-1), and requires bits within 0.1 % and PSNR within
-    0.01 dB (north_star).  Counts go to gpurun_out/e2e_fp32_*.json.
-bf16 (tcgen05) mode: encoder/decoder agree with each other exactly; rate / quality deltas against
-the fp32 goldens are reported and bounded.
+    0.01 dB (north_star).  Counts go to gpurun_out/e2e_<mode>_*.json.
+  * cfg1_240x416 free-running I + 2 P chain against the reference goldens: symbol flips and stream
+    equality are reported as first-class numbers, bits within 0.1 % and PSNR within 0.01 dB asserted.
+  * one teacher-forced 1920x1088 P-frame against the oracle (parity mode; slow: the CPU oracle).
+bf16 (tcgen05) mode: encoder/decoder agree with each other exactly; symbol-mismatch rates against the
+fp32 goldens are bounded by stated ceilings; the north_star bpp / PSNR bounds are checked in a separate
+test that is EXPECTED to fail for plain bf16 operands (xfail, non-strict) so the gap stays visible.
 """
 import json
 import math
@@ -66,15 +76,29 @@ def bf16_models():
     return _models("bf16")
 
 
+@pytest.fixture(scope="module")
+def parity_models():
+    return _models("parity")
+
+
+@pytest.fixture(scope="module")
+def exact_models(request, fp32_models, parity_models):
+    return {"fp32": fp32_models, "parity": parity_models}
+
+
+EXACT_MODES = ["fp32", "parity"]
+
+
 def _report(name, obj):
     os.makedirs(os.path.join(ROOT, "gpurun_out"), exist_ok=True)
     with open(os.path.join(ROOT, "gpurun_out", name), "w") as f:
         json.dump(obj, f, indent=1)
 
 
-def test_fp32_mode_bit_exact_chain_tiny(fp32_models, golden_dir, tmp_path):
+@pytest.mark.parametrize("mode", EXACT_MODES)
+def test_exact_modes_bit_exact_chain_tiny(exact_models, mode, golden_dir, tmp_path):
     from oracle import dcvc_oracle as O
-    dmc, intra = fp32_models
+    dmc, intra = exact_models[mode]
     G = np.load(os.path.join(golden_dir, "tiny_64x128.npz"))
     ph, pw, qi, qmv, qy = G["meta"]
     ph, pw = int(ph), int(pw)
@@ -111,7 +135,7 @@ def test_fp32_mode_bit_exact_chain_tiny(fp32_models, golden_dir, tmp_path):
         for k in ("ref_y", "ref_mv_y", "ref_feature"):
             assert torch.equal(d[k], enc["dbp"][k]), k
         dpb = d
-    _report("e2e_fp32_tiny.json", rep)
+    _report(f"e2e_{mode}_tiny.json", rep)
     # scale indexes: identical streams prove the coded CDF rows agree; an index may still differ by
     # one where log(sigma) sits on a bin edge and both rows quantise to the same CDF
     assert sum(rep.values()) <= 2, rep
@@ -122,10 +146,11 @@ def _flip_stats(mine, gold):
     return int((d != 0).sum()), int(np.abs(d).max()) if d.size else 0
 
 
-def test_fp32_mode_teacher_forced_cfg1(fp32_models, golden_dir):
+@pytest.mark.parametrize("mode", EXACT_MODES)
+def test_exact_modes_teacher_forced_cfg1(exact_models, mode, golden_dir):
     """416x240 (padded 448x256): GPU vs the oracle, each frame fed the oracle's own dpb."""
     from oracle import dcvc_oracle as O
-    dmc, intra = fp32_models
+    dmc, intra = exact_models[mode]
     sd_p, sd_i = _state_dicts()
     torch.set_num_threads(min(8, os.cpu_count() or 1))
     odmc, ointra = O.OracleDMC(sd_p), O.OracleIntra(sd_i)
@@ -176,18 +201,123 @@ def test_fp32_mode_teacher_forced_cfg1(fp32_models, golden_dir):
         rep[p + "psnr_delta_db"] = abs(_psnr(x, gres["dpb"]["ref_frame"].cpu()) - _psnr(x, ores["dpb"]["ref_frame"]))
         rep[p + "stream_equal"] = genc["bit_stream"] == oenc["bit_stream"]
         odpb = ores["dpb"]
-    _report("e2e_fp32_cfg1.json", rep)
-    print(rep)
+    _report(f"e2e_{mode}_cfg1.json", rep)
+    print(mode, rep)
     for pre in ("i_", "p1_", "p2_"):
         assert rep[pre + "flip_rate"] <= 2e-4, rep
         assert rep[pre + "bits_rel"] <= 1e-3, rep
         assert rep[pre + "psnr_delta_db"] <= 0.01, rep
 
 
+_FREE_RUNNING = {}
+
+
+@pytest.mark.parametrize("mode", EXACT_MODES)
+def test_exact_modes_free_running_cfg1(exact_models, mode, golden_dir):
+    """416x240 free-running I + 2 P chain (every frame predicted from the GPU's own previous
+    reconstruction) against the goldens written by the unmodified reference.  Symbol flips, scale-index
+    mismatches and stream equality are reported (gpurun_out/e2e_<mode>_cfg1_free.json); bits within 0.1 %
+    and PSNR within 0.01 dB of the reference are asserted (north_star), and the tensor-core parity mode must
+    take exactly the decisions of the fp32-FMA mode over the whole chain."""
+    from oracle import dcvc_oracle as O
+    dmc, intra = exact_models[mode]
+    G = np.load(os.path.join(golden_dir, "cfg1_240x416.npz"))
+    ph, pw, qi, qmv, qy = G["meta"]
+    ph, pw = int(ph), int(pw)
+    fr = torch.from_numpy(G["frames_u8"])
+    x0 = _pad64(fr[0:1].float() / 255.0).cuda()
+    rep = {"mode": mode}
+    r, blob = intra.encode_decode_bytes(x0, qi, ph, pw)
+    flips = total = 0          # the goldens hold no I-frame symbol planes: its .bin is compared instead
+    rep["i_stream_equal"] = blob == G["i_bin"].tobytes()
+    rep["i_bits_rel"] = abs(r["bit"] - int(G["i_bit"][0])) / int(G["i_bit"][0])
+    rep["i_psnr_delta_db"] = abs(_psnr(x0.cpu(), r["x_hat"].cpu()) - _psnr(x0.cpu(), torch.from_numpy(G["i_x_hat"])))
+    dpb = {"ref_frame": r["x_hat"], "ref_feature": None, "ref_y": None, "ref_mv_y": None}
+    for t in (1, 2):
+        p = f"p{t}_"
+        x = _pad64(fr[t:t + 1].float() / 255.0).cuda()
+        mvq, _ = O.get_rounded_q(qmv)
+        yq, _ = O.get_rounded_q(qy)
+        enc = dmc.compress(x, dpb, mvq, yq)
+        S = dmc._last_symbols
+        for mine, gold in SYMS:
+            n, mx = _flip_stats(S[mine].numpy(), G[p + gold])
+            rep[p + gold + "_flips"] = n
+            flips += n
+            total += G[p + gold].size
+        for mine, gold in IDXS:
+            rep[p + gold + "_mismatch"] = int((S[mine].numpy() != G[p + gold]).sum())
+        rep[p + "stream_equal"] = enc["bit_stream"] == G[p + "stream"].tobytes()
+        res, blob = dmc.encode_decode_bytes(x, dpb, ph, pw, qmv, qy)
+        rep[p + "bin_equal"] = blob == G[p + "bin"].tobytes()
+        rep[p + "bits_rel"] = abs(res["bit"] - int(G[p + "bit"][0])) / int(G[p + "bit"][0])
+        rep[p + "psnr_delta_db"] = abs(_psnr(x.cpu(), res["dpb"]["ref_frame"].cpu()) -
+                                       _psnr(x.cpu(), torch.from_numpy(G[p + "ref_frame"])))
+        dpb = res["dpb"]
+    rep["symbol_flips_total"] = flips
+    rep["symbols_total"] = int(total)
+    _report(f"e2e_{mode}_cfg1_free.json", rep)
+    print(mode, rep)
+    for pre in ("i_", "p1_", "p2_"):
+        assert rep[pre + "bits_rel"] <= 1e-3, rep
+        assert rep[pre + "psnr_delta_db"] <= 0.01, rep
+    # Flips are REPORTED, not bounded, here: on this fixture ONE I-frame symbol (of 91 392) sits within float
+    # noise of a rounding boundary and lands on the other side than the reference's oneDNN summation order put
+    # it (the same single flip in the fp32-FMA mode and in the tensor-core parity mode); from then on the chain
+    # predicts from a legitimately different reconstruction, so later symbols differ without any further
+    # arithmetic disagreement (teacher-forced: 0 P-frame flips, streams byte-equal).  What must hold is that
+    # both exact modes make the SAME decisions:
+    _FREE_RUNNING[mode] = {k: v for k, v in rep.items() if k.endswith("_flips") or k.endswith("_mismatch")}
+    if len(_FREE_RUNNING) == 2:
+        assert _FREE_RUNNING["fp32"] == _FREE_RUNNING["parity"], _FREE_RUNNING
+
+
+@pytest.mark.slow
+def test_parity_mode_teacher_forced_1080p_p_frame(parity_models):
+    """BASELINE shape: one 1920x1088 P-frame (reference frame = a synthetic neighbour frame), GPU
+    tensor-core parity mode against the CPU oracle on the same inputs: symbol flips reported and bounded
+    (<= 2e-4, each by +-1), bits within 0.1 %.  ~1-2 minutes of CPU oracle."""
+    from oracle import dcvc_oracle as O
+    import bench as Bn
+    dmc, _ = parity_models
+    sd_p, _ = _state_dicts()
+    torch.set_num_threads(os.cpu_count() or 1)
+    odmc = O.OracleDMC(sd_p)
+    odmc.update()
+    seq = Bn.synth_sequence(2, 5)
+    pad = lambda x: torch.nn.functional.pad(x, (0, Bn.WP - Bn.W, 0, Bn.HP - Bn.H))  # noqa: E731
+    ref, x = pad(seq[0:1]), pad(seq[1:2])
+    odpb = {"ref_frame": ref, "ref_feature": None, "ref_y": None, "ref_mv_y": None}
+    oenc = odmc.compress(x, odpb, 1.0, 1.0, want_symbols=True)
+    gdpb = {"ref_frame": ref.cuda(), "ref_feature": None, "ref_y": None, "ref_mv_y": None}
+    genc = dmc.compress(x.cuda(), gdpb, 1.0, 1.0)
+    rep, tot, flips = {}, 0, 0
+    for k, _ in SYMS:
+        n, mx = _flip_stats(dmc._last_symbols[k].numpy(), oenc["symbols"][k].numpy())
+        rep[k + "_flips"] = n
+        assert mx <= 1, (k, mx)
+        flips += n
+        tot += oenc["symbols"][k].numel()
+    rep["flip_rate"] = flips / tot
+    rep["symbols"] = tot
+    rep["stream_equal"] = genc["bit_stream"] == oenc["bit_stream"]
+    rep["bits_rel"] = abs(len(genc["bit_stream"]) - len(oenc["bit_stream"])) / len(oenc["bit_stream"])
+    rep["recon_max_abs_diff"] = (genc["dbp"]["ref_frame"].cpu() - oenc["dbp"]["ref_frame"]).abs().max().item()
+    _report("e2e_parity_1080p.json", rep)
+    print(rep)
+    assert tot == 1370880
+    assert rep["flip_rate"] <= 2e-4 and rep["bits_rel"] <= 1e-3, rep
+
+
+_BF16_REPORT = {}
+
+
 def test_bf16_mode_self_consistent_and_close(bf16_models, golden_dir):
-    """tcgen05 mode: streams decode to exactly what the encoder reconstructed; rate / quality stay
-    within 1 % bpp and 0.1 dB of the fp32 reference goldens on the fixture (the north_star bounds
-    of 0.1 % / 0.01 dB are reported in gpurun_out/e2e_bf16.json)."""
+    """Plain-bf16 tcgen05 mode: streams decode to exactly what the encoder reconstructed (the mode is
+    self-decodable ONLY: its streams are not the reference's).  Against the fp32 reference goldens the
+    symbol-mismatch rate is bounded by stated ceilings (15 % of the latent symbols, 60 % of the scale
+    indexes) and rate / quality by 1 % bpp / 0.1 dB; the north_star bounds (0.1 % / 0.01 dB, bit-exact
+    symbols) are NOT met by this mode -- see test_bf16_mode_north_star_bounds and the parity mode."""
     from oracle import dcvc_oracle as O
     dmc, intra = bf16_models
     G = np.load(os.path.join(golden_dir, "cfg1_240x416.npz"))
@@ -219,11 +349,35 @@ def test_bf16_mode_self_consistent_and_close(bf16_models, golden_dir):
         rep[p + "psnr_delta_db"] = abs(_psnr(x.cpu(), res["dpb"]["ref_frame"].cpu()) -
                                        _psnr(x.cpu(), torch.from_numpy(G[p + "ref_frame"])))
         dpb = res["dpb"]
+    for t in (1, 2):
+        sm = sum(rep[f"p{t}_{g}_mismatch"] for _, g in SYMS)
+        st = sum(rep[f"p{t}_{g}_total"] for _, g in SYMS)
+        im = sum(rep[f"p{t}_{g}_mismatch"] for _, g in IDXS)
+        it = sum(rep[f"p{t}_{g}_total"] for _, g in IDXS)
+        rep[f"p{t}_symbol_mismatch_rate"] = sm / st
+        rep[f"p{t}_index_mismatch_rate"] = im / it
     _report("e2e_bf16.json", rep)
+    _BF16_REPORT.update(rep)
     print(rep)
     assert rep["i_bits_rel"] < 0.01 and rep["i_psnr_delta_db"] < 0.1
     for t in (1, 2):
         assert rep[f"p{t}_bits_rel"] < 0.01 and rep[f"p{t}_psnr_delta_db"] < 0.1
+        assert rep[f"p{t}_symbol_mismatch_rate"] < 0.15, rep
+        assert rep[f"p{t}_index_mismatch_rate"] < 0.60, rep
+
+
+@pytest.mark.xfail(reason="plain bf16 operands cannot meet north_star's 0.1 % bpp / bit-exact-symbol bounds "
+                          "(measured: P1 bpp off by ~0.17 %, 1-9 % of symbols differ); precision='parity' is the "
+                          "tensor-core mode that does", strict=False)
+def test_bf16_mode_north_star_bounds(bf16_models, golden_dir):
+    if not _BF16_REPORT:
+        test_bf16_mode_self_consistent_and_close(bf16_models, golden_dir)
+    rep = _BF16_REPORT
+    for pre in ("i_", "p1_", "p2_"):
+        assert rep[pre + "bits_rel"] <= 1e-3, rep
+        assert rep[pre + "psnr_delta_db"] <= 0.01, rep
+    for t in (1, 2):
+        assert rep[f"p{t}_symbol_mismatch_rate"] == 0.0, rep
 
 
 def test_batched_estimation_path(fp32_models):

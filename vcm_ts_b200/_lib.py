@@ -13,7 +13,7 @@ SO = os.path.join(HERE, "libvcmts_b200.so")
 
 F32, BF16 = 0, 1
 CONV_PRE_ACT, CONV_POST_ACT, CONV_PIXEL_SHUFFLE = 1, 2, 4
-CONV_RES, CONV_RES_SCALE, CONV_RES2, CONV_OUT2 = 8, 16, 32, 64
+CONV_RES, CONV_RES_SCALE, CONV_RES2, CONV_OUT2, CONV_SPLIT3 = 8, 16, 32, 64, 128
 
 
 class ConvDesc(Structure):
@@ -23,7 +23,7 @@ class ConvDesc(Structure):
                 ("out2_cstride", c_int32),
                 ("flags", c_int32), ("pre_slope", c_float), ("post_slope", c_float),
                 ("out2_slope", c_float),
-                ("in_dtype", c_int32), ("out_dtype", c_int32)]
+                ("in_dtype", c_int32), ("out_dtype", c_int32), ("in_pstride", c_int32)]
 
 
 class DpDesc(Structure):
@@ -44,10 +44,9 @@ _PROTOS = {
     "vcm_conv2d_tc_weight_bytes": (c_int64, [c_int32, c_int32, c_int32]),
     "vcm_pack_conv_weight_umma": (c_int, [_P, _P, c_int32, c_int32, c_int32, c_int32, _P, _P]),
     "vcm_conv2d_tc_fwd": (c_int, [POINTER(ConvDesc), _P, _P, _P, _P, _P, _P, _P, _P, _P]),
-    "vcm_umma_probe": (c_int, [c_int32, c_int32, c_int32, _P, _P]),
-    "vcm_umma_rate": (c_int, [c_int32, c_int32, _P, _P]),
-    "vcm_umma_rate2": (c_int, [c_int32, c_int32, c_int32, c_int32, _P, _P]),
-    "vcm_tma_probe": (c_int, [_P, c_int32, c_int32, c_int32, c_int32, c_int32, c_int32, _P, _P]),
+    "vcm_split_bf16x3": (c_int, [_P, _P, c_int64, c_int32, c_int32, c_int32, c_int32, c_int32, c_int32,
+                                 c_float, _P]),
+    "vcm_pack_conv_weight_umma_split3": (c_int, [_P, _P, c_int32, c_int32, c_int32, c_int32, _P, _P]),
     "vcm_nchw_to_nhwc": (c_int, [_P, _P, c_int32, c_int32, c_int32, c_int32, c_int32, c_int32, _P]),
     "vcm_u8hwc_to_frame": (c_int, [_P, _P, c_int32, c_int32, c_int32, c_int32, c_int32, _P]),
     "vcm_frame_to_u8hwc": (c_int, [_P, _P, c_int32, c_int32, c_int32, c_int32, c_int32, _P]),

@@ -54,15 +54,21 @@ def _code(dtype):
 
 class PackedConv:
     """Device-side packed weights of one nn.Conv2d (fp32 [tap][Cin_p][Cout] + optional UMMA bf16)."""
-    __slots__ = ("w", "bias", "K", "Cin", "Cout", "w_umma", "bias_tc", "ps")
+    __slots__ = ("w", "bias", "K", "Cin", "Cout", "w_umma", "bias_tc", "ps", "cin_tc")
 
     def __init__(self, w, bias, K, Cin, Cout, w_umma=None):
         self.w, self.bias, self.K, self.Cin, self.Cout, self.w_umma = w, bias, K, Cin, Cout, w_umma
-        self.bias_tc, self.ps = bias, False
+        self.bias_tc, self.ps, self.cin_tc = bias, False, Cin
+
+
+PRECISIONS = ("fp32", "bf16", "parity")
 
 
 class CudaBackend:
-    """precision: 'fp32' (exact mode, fp32 FMA convs) or 'bf16' (tcgen05 tensor-core convs)."""
+    """precision: 'fp32' (exact mode, fp32 FMA convs on CUDA cores), 'bf16' (tcgen05 tensor-core convs,
+    bf16 activations) or 'parity' (tcgen05 convs on split-bf16 operands: fp32 activations in HBM, every
+    conv input split into three bf16 planes and every weight into three bf16 parts, six MMAs per
+    product -> fp32-class accuracy on the tensor pipe; the graph is the exact mode's)."""
 
     def __init__(self, device, precision="fp32"):
         self.L = _lib.lib()
@@ -72,10 +78,10 @@ class CudaBackend:
         with torch.cuda.device(self.device):
             if not self.L.vcm_device_ok():
                 raise RuntimeError("libvcmts_b200.so: no compute-capability-10.x device visible")
-        if precision not in ("fp32", "bf16"):
-            raise ValueError("precision must be 'fp32' or 'bf16'")
+        if precision not in PRECISIONS:
+            raise ValueError("precision must be one of %s" % (PRECISIONS,))
         self.precision = precision
-        self.act_dtype = torch.float32 if precision == "fp32" else torch.bfloat16
+        self.act_dtype = torch.bfloat16 if precision == "bf16" else torch.float32
         # bf16 mode: producers also store the activated twin a following ResBlock reads, so the
         # tensor-core engine never needs a pre-activation on TMA-loaded tiles
         self.use_twin = precision == "bf16"
@@ -109,6 +115,25 @@ class CudaBackend:
                                           m.data_ptr() if m is not None else None, self.stream),
               "vcm_pack_conv_weight")
         pc = PackedConv(out, bias.detach().to(self.device, torch.float32).contiguous(), K, cin_p, Cout)
+        if self.precision == "parity":
+            # three bf16 parts of the fp32 weights, input channels padded to 16 (zero rows)
+            cp = (cin_p + 15) // 16 * 16
+            nbytes = self.L.vcm_conv2d_tc_weight_bytes(Cout, cp, K)
+            if nbytes > 0:
+                full = list(in_map) if in_map is not None else list(range(Cin))
+                full = full + [-1] * (cp - len(full))
+                m3 = torch.tensor(full, dtype=torch.int32, device=self.device)
+                wu = torch.empty((3 * nbytes,), dtype=torch.uint8, device=self.device)
+                if ps:
+                    assert Cout % 4 == 0
+                    perm = torch.arange(Cout, device=self.device).reshape(Cout // 4, 4).t().reshape(-1)
+                    w = w[perm].contiguous()
+                    pc.bias_tc = pc.bias[perm].contiguous()
+                    pc.ps = True
+                check(self.L.vcm_pack_conv_weight_umma_split3(w.data_ptr(), wu.data_ptr(), Cout, Cin, K, cp,
+                                                              m3.data_ptr(), self.stream),
+                      "vcm_pack_conv_weight_umma_split3")
+                pc.w_umma, pc.cin_tc = wu, cp
         if self.precision == "bf16" and cin_p % 16 == 0:
             nbytes = self.L.vcm_conv2d_tc_weight_bytes(Cout, cin_p, K)
             if nbytes > 0:
@@ -170,12 +195,39 @@ class CudaBackend:
                 res_scale.data_ptr() if res_scale is not None else None,
                 res2.ptr if res2 is not None else None, out.ptr,
                 out2.ptr if slope2 is not None else None, self.stream]
-        if pc.w_umma is not None and self.L.vcm_conv2d_tc_supported(ctypes.byref(d)) == 1:
+        if self.precision == "parity" and pc.w_umma is not None and x.dtype == torch.float32:
+            # split the fp32 input (pre-activation applied on the way) into three bf16 planes and run
+            # the tensor-core engine on them; the epilogue works in fp32 as in the exact mode
+            cp = pc.cin_tc
+            d3 = ConvDesc(x.N, x.H, x.W, cp, pc.Cout, K, stride, 3 * cp, out.cs,
+                          res.cs if res is not None else 0, res2.cs if res2 is not None else 0,
+                          out2.cs if slope2 is not None else 0,
+                          (flags & ~_lib.CONV_PRE_ACT) | _lib.CONV_SPLIT3,
+                          0.0, float(post or 0.0), float(slope2 or 0.0), BF16, _code(out.dtype), cp)
+            if self.L.vcm_conv2d_tc_supported(ctypes.byref(d3)) == 1:
+                if pc.ps != bool(ps):
+                    raise RuntimeError("conv weights were packed for ps=%s but the conv is launched with ps=%s"
+                                       % (pc.ps, bool(ps)))
+                xs = torch.empty((x.N, x.H, x.W, 3 * cp), dtype=torch.bfloat16, device=self.device)
+                check(self.L.vcm_split_bf16x3(x.ptr, xs.data_ptr(), x.N * x.H * x.W, x.C, cp, x.cs, 3 * cp, cp,
+                                              1 if pre is not None else 0, float(pre or 0.0), self.stream),
+                      "vcm_split_bf16x3")
+                args[0], args[1] = ctypes.byref(d3), xs.data_ptr()
+                args[2], args[3] = pc.w_umma.data_ptr(), pc.bias_tc.data_ptr()
+                check(self.L.vcm_conv2d_tc_fwd(*args), "vcm_conv2d_tc_fwd")
+                self.launches += 2
+                return (out, out2) if slope2 is not None else out
+        if self.precision == "bf16" and pc.w_umma is not None and \
+                self.L.vcm_conv2d_tc_supported(ctypes.byref(d)) == 1:
             if pc.ps != bool(ps):
                 raise RuntimeError("conv weights were packed for ps=%s but the conv is launched with ps=%s"
                                    % (pc.ps, bool(ps)))
             args[2], args[3] = pc.w_umma.data_ptr(), pc.bias_tc.data_ptr()
-            check(self.L.vcm_conv2d_tc_fwd(*args), "vcm_conv2d_tc_fwd")
+            rc = self.L.vcm_conv2d_tc_fwd(*args)
+            if rc == 2 and not pc.ps:     # e.g. a view whose base is not 16-byte aligned: fp32-FMA engine
+                args[2], args[3] = pc.w.data_ptr(), pc.bias.data_ptr()
+                rc = self.L.vcm_conv2d_fwd(*args)
+            check(rc, "vcm_conv2d_tc_fwd")
         else:
             args[2] = pc.w.data_ptr()
             check(self.L.vcm_conv2d_fwd(*args), "vcm_conv2d_fwd")

@@ -30,7 +30,24 @@ def stale():
     return any(os.path.getmtime(p) > t for p in deps)
 
 
+PROBE_SRC = os.path.join(CSRC, "probe", "tc_probe.cu")
+PROBE_OUT = os.path.join(HERE, "libvcmts_probe.so")
+
+
+def build_probe(force=False):
+    """libvcmts_probe.so: hardware probes (diagnostics; not part of the product library)."""
+    deps = [PROBE_SRC] + glob.glob(os.path.join(CSRC, "*.cuh")) + \
+        glob.glob(os.path.join(HERE, "..", "include", "*.h"))
+    if not force and os.path.exists(PROBE_OUT) and \
+            all(os.path.getmtime(p) <= os.path.getmtime(PROBE_OUT) for p in deps):
+        return PROBE_OUT
+    subprocess.check_call([NVCC, *FLAGS, "-shared", PROBE_SRC, "-o", PROBE_OUT, "-lcudart"],
+                          stderr=subprocess.DEVNULL)
+    return PROBE_OUT
+
+
 def build(force=False, verbose=False):
+    build_probe(force)
     if not force and not stale():
         return OUT
     objs = []

@@ -35,6 +35,11 @@ constexpr int H_THREADS = 384;
 constexpr int H_MAX_A = 6, H_MAX_B = 12, H_MAX_ACC = 4;
 
 struct HaloGeom {
+  // split-bf16 parity mode (VCM_CONV_SPLIT3): split = 1, an activation stage holds the THREE bf16 planes
+  // of one Cin chunk (a_plane_bytes apart), weight slabs are [part][tap][chunk], and an item owns
+  // nsacc TMEM accumulators of bn columns: [0] = the correction terms (x_i*w_j, i+j > 0), [1..] = the
+  // main term x0*w0 dealt round-robin over (chunk, tap) -- summed in fp32 by the epilogue
+  int split, pstride, a_plane_bytes, nsacc;
   int nchunks, ntaps, a_stages, b_stages, resident;
   int a_bytes, a_stage_bytes;
   int b_bytes, b_slot_bytes, b_base;
@@ -129,6 +134,98 @@ __device__ __forceinline__ void mma_role(const HaloGeom& G, const HaloBars& B, u
   }
 }
 
+
+// Split-bf16 (parity) MMA role.  The tensor core's fp32 accumulate truncates (measured: the error of a long
+// accumulation chain grows linearly, profiles/umma_acc_probe_r02.json), so
+//   * the main term x0*w0 -- whose bf16 x bf16 products are exact in fp32 -- is spread over several
+//     accumulators (short chains), and
+//   * the five correction terms (2^-8 / 2^-16 of the main term) get their own accumulator, so that they
+//     are not truncated at the main sum's ulp.
+// The epilogue adds the accumulators with round-to-nearest fp32 adds.  One stage = three planes of one Cin
+// chunk; for every weight slab (part j, tap) the planes i <= 2 - j are multiplied: 6 products, 3 slabs.
+template <int CHUNK, int K, bool RESIDENT>
+__device__ __forceinline__ void mma_role_split(const HaloGeom& G, const HaloBars& B, uint32_t a_smem,
+                                               uint32_t b_smem, uint32_t tmem_base) {
+  constexpr uint32_t LAYOUT = CHUNK == 64 ? 2u : (CHUNK == 32 ? 4u : 6u);
+  constexpr uint32_t ROWB = CHUNK * 2u;
+  constexpr int KSTEPS = CHUNK / 16;
+  constexpr uint32_t HW = HTW + K - 1;
+  constexpr uint32_t AROW16 = ROWB >> 4;
+  constexpr uint32_t ALINE16 = (HW * ROWB) >> 4;
+  int as = 0, bs = 0, acc = 0;
+  uint32_t aphase = 0, bphase = 0, acc_phase = 0;
+  bool first = true;
+  const uint64_t bdesc0 = make_smem_desc(b_smem, 8u * ROWB, LAYOUT);
+  const uint32_t bslot16 = (uint32_t)G.b_slot_bytes >> 4;
+  const uint32_t btap16 = bslot16 * (uint32_t)G.nchunks;
+  const uint32_t bpart16 = btap16 * (uint32_t)G.ntaps;
+  const uint32_t aplane16 = (uint32_t)G.a_plane_bytes >> 4;
+  const uint32_t idesc = G.idesc;
+  const uint32_t bn = (uint32_t)G.bn;
+  const int nmain = G.nsacc - 1;
+  for (int item = blockIdx.x; item < G.num_items; item += gridDim.x) {
+    mbar_wait(&B.tempty[acc], acc_phase ^ 1u);
+    tc_fence_after();
+    const uint32_t d_tmem = tmem_base + (uint32_t)acc * (uint32_t)G.nsacc * bn;
+    uint32_t started = 0;   // accumulators already written for this item (elected lane only)
+    int mctr = 0;           // main-term slab counter -> accumulator 1 + mctr % nmain
+    for (int ch = 0; ch < G.nchunks; ++ch) {
+      mbar_wait(&B.afull[as], aphase);
+      tc_fence_after();
+      if (elect_one()) {
+        const uint64_t adesc0 = make_smem_desc(a_smem + (uint32_t)as * (uint32_t)G.a_stage_bytes, HW * ROWB, LAYOUT);
+        for (int pj = 2; pj >= 0; --pj) {
+          const uint64_t bch = bdesc0 + (uint64_t)((uint32_t)ch * bslot16 + (uint32_t)pj * bpart16);
+#pragma unroll
+          for (int ky = 0; ky < K; ++ky) {
+#pragma unroll
+            for (int kx = 0; kx < K; ++kx) {
+              const int tap = ky * K + kx;
+              uint64_t bdesc;
+              if (RESIDENT) {
+                if (first) {
+                  mbar_wait(&B.bfull[tap < H_MAX_B - 1 ? tap : H_MAX_B - 1], 0);
+                  tc_fence_after();
+                }
+                bdesc = bch + (uint64_t)((uint32_t)tap * btap16);
+              } else {
+                mbar_wait(&B.bfull[bs], bphase);
+                tc_fence_after();
+                bdesc = bdesc0 + (uint64_t)((uint32_t)bs * bslot16);
+              }
+              const uint64_t atap = adesc0 + (uint64_t)(ky * ALINE16 + kx * AROW16);
+              for (int pi = 0; pi <= 2 - pj; ++pi) {
+                uint32_t sel = 0;
+                if (pi == 0 && pj == 0) {
+                  sel = 1u + (uint32_t)mctr;
+                  if (++mctr == nmain) mctr = 0;
+                }
+                const uint32_t d = d_tmem + sel * bn;
+                const uint64_t adesc = atap + (uint64_t)((uint32_t)pi * aplane16);
+#pragma unroll
+                for (int k = 0; k < KSTEPS; ++k)
+                  umma_bf16(d, adesc + (uint64_t)(2 * k), bdesc + (uint64_t)(2 * k), idesc,
+                            k > 0 ? 1u : ((started >> sel) & 1u));
+                started |= 1u << sel;
+              }
+              if (!RESIDENT) {
+                umma_commit(&B.bempty[bs]);
+                if (++bs == G.b_stages) { bs = 0; bphase ^= 1u; }
+              }
+            }
+          }
+        }
+        umma_commit(&B.aempty[as]);
+        if (ch == G.nchunks - 1) umma_commit(&B.tfull[acc]);
+      }
+      first = false;
+      __syncwarp();
+      if (++as == G.a_stages) { as = 0; aphase ^= 1u; }
+    }
+    if (++acc == G.nacc) { acc = 0; acc_phase ^= 1u; }
+  }
+}
+
 template <int CHUNK>
 __global__ void __launch_bounds__(H_THREADS, 1)
 conv_halo_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
@@ -185,9 +282,16 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         const int y0 = (rem / G.tiles_x) * (HTH * G.mh), x0 = (rem % G.tiles_x) * HTW;
         for (int ch = 0; ch < G.nchunks; ++ch) {
           mbar_wait(&aempty[stage], phase ^ 1u);
-          mbar_expect_tx(&afull[stage], (uint32_t)G.a_bytes);
-          tma_load_4d(smem_u32(smem + (size_t)stage * G.a_stage_bytes), &tmA, &afull[stage], ch * CHUNK,
-                      x0 - P.pad, y0 - P.pad, n);
+          const uint32_t dst = smem_u32(smem + (size_t)stage * G.a_stage_bytes);
+          if (G.split) {
+            mbar_expect_tx(&afull[stage], 3u * (uint32_t)G.a_bytes);
+            for (int p = 0; p < 3; ++p)
+              tma_load_4d(dst + (uint32_t)(p * G.a_plane_bytes), &tmA, &afull[stage], p * G.pstride + ch * CHUNK,
+                          x0 - P.pad, y0 - P.pad, n);
+          } else {
+            mbar_expect_tx(&afull[stage], (uint32_t)G.a_bytes);
+            tma_load_4d(dst, &tmA, &afull[stage], ch * CHUNK, x0 - P.pad, y0 - P.pad, n);
+          }
           if (++stage == G.a_stages) { stage = 0; phase ^= 1u; }
         }
       }
@@ -195,6 +299,7 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   } else if (warp == 2) {
     // ============================ weight producer ==============================================
     if (lane == 0) {
+      const int nparts = G.split ? 3 : 1;
       if (G.resident) {
         // one barrier per tap (the taps past H_MAX_B - 1 share the last one), in the order the MMA role
         // consumes them: the first tile starts after 1/ntaps of the weights has landed, not all of them
@@ -202,11 +307,12 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
           const int bi = tap < H_MAX_B - 1 ? tap : H_MAX_B - 1;
           if (tap <= H_MAX_B - 1)
             mbar_expect_tx(&bfull[bi], (uint32_t)((tap < H_MAX_B - 1 ? 1 : G.ntaps - (H_MAX_B - 1)) * G.nchunks *
-                                                  G.b_bytes));
-          for (int ch = 0; ch < G.nchunks; ++ch) {
-            const int s = tap * G.nchunks + ch;
-            tma_load_2d(smem_u32(smem + G.b_base + (size_t)s * G.b_slot_bytes), &tmB, &bfull[bi], 0, s * G.cout_p);
-          }
+                                                  nparts * G.b_bytes));
+          for (int part = 0; part < nparts; ++part)
+            for (int ch = 0; ch < G.nchunks; ++ch) {
+              const int s = (part * G.ntaps + tap) * G.nchunks + ch;   // slab layout [part][tap][chunk]
+              tma_load_2d(smem_u32(smem + G.b_base + (size_t)s * G.b_slot_bytes), &tmB, &bfull[bi], 0, s * G.cout_p);
+            }
         }
       } else {
         int stage = 0;
@@ -214,13 +320,14 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         for (int item = blockIdx.x; item < G.num_items; item += gridDim.x) {
           const int nt = item % G.n_tiles;
           for (int ch = 0; ch < G.nchunks; ++ch)
-            for (int tap = 0; tap < G.ntaps; ++tap) {
-              mbar_wait(&bempty[stage], phase ^ 1u);
-              mbar_expect_tx(&bfull[stage], (uint32_t)G.b_bytes);
-              tma_load_2d(smem_u32(smem + G.b_base + (size_t)stage * G.b_slot_bytes), &tmB, &bfull[stage], 0,
-                          (tap * G.nchunks + ch) * G.cout_p + nt * G.bn);
-              if (++stage == G.b_stages) { stage = 0; phase ^= 1u; }
-            }
+            for (int part = nparts - 1; part >= 0; --part)     // the order the MMA role consumes them
+              for (int tap = 0; tap < G.ntaps; ++tap) {
+                mbar_wait(&bempty[stage], phase ^ 1u);
+                mbar_expect_tx(&bfull[stage], (uint32_t)G.b_bytes);
+                tma_load_2d(smem_u32(smem + G.b_base + (size_t)stage * G.b_slot_bytes), &tmB, &bfull[stage], 0,
+                            ((part * G.ntaps + tap) * G.nchunks + ch) * G.cout_p + nt * G.bn);
+                if (++stage == G.b_stages) { stage = 0; phase ^= 1u; }
+              }
         }
       }
     }
@@ -230,7 +337,9 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     const uint32_t a_smem = smem_u32(smem), b_smem = smem_u32(smem + G.b_base);
 #define HALO_MMA(KK)                                                                              \
   do {                                                                                            \
-    if (G.resident) mma_role<CHUNK, KK, 1, true>(G, B, a_smem, b_smem, tmem_base);                 \
+    if (G.split && G.resident) mma_role_split<CHUNK, KK, true>(G, B, a_smem, b_smem, tmem_base);   \
+    else if (G.split) mma_role_split<CHUNK, KK, false>(G, B, a_smem, b_smem, tmem_base);           \
+    else if (G.resident) mma_role<CHUNK, KK, 1, true>(G, B, a_smem, b_smem, tmem_base);            \
     else if (G.mh == 1) mma_role<CHUNK, KK, 1, false>(G, B, a_smem, b_smem, tmem_base);            \
     else mma_role<CHUNK, KK, 2, false>(G, B, a_smem, b_smem, tmem_base);                           \
   } while (0)
@@ -256,10 +365,15 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       const int cbase = nt * G.bn;
       for (int h = 0; h < G.mh; ++h) {
         const int oy0 = (rem / G.tiles_x) * (HTH * G.mh) + h * HTH;
-        const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)((ab * G.mh + h) * G.bn);
+        const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) +
+                               (uint32_t)(G.split ? ab * G.nsacc * G.bn : (ab * G.mh + h) * G.bn);
         uint64_t* wait = h == 0 ? &tfull[ab] : nullptr;
         uint64_t* release = h == G.mh - 1 ? &tempty[ab] : nullptr;
-        if (G.scalar_epi == 0) {
+        if (G.split) {
+          const int m = q * 32 + lane;
+          epilogue_thread_scalar<float>(P, G.bn, n, oy0 + m / HTW, ox0 + m % HTW, cbase, taddr, wait, acc_phase,
+                                        release, G.nsacc);
+        } else if (G.scalar_epi == 0) {
           if (G.epi_bw == 32)
             epilogue_warp_vec<32, HTW>(P, G.bn, n, oy0, ox0, cbase, taddr, stage, q, lane, wait, acc_phase, release, bias_smem);
           else
@@ -297,8 +411,10 @@ int vcm_conv_halo_launch(const vcm_conv_desc* d, const ConvParams& P, const void
   }
   HaloGeom G;
   memset(&G, 0, sizeof(G));
-  const int chunk = pick_chunk(P.Cin);
-  pick_n_tiling(P.Cout, G.cout_p, G.bn, G.n_tiles);
+  G.split = (P.flags & VCM_CONV_SPLIT3) ? 1 : 0;
+  G.pstride = d->in_pstride;
+  const int chunk = G.split ? pick_chunk_split(P.Cin, P.K) : pick_chunk(P.Cin);
+  pick_n_tiling(P.Cout, G.cout_p, G.bn, G.n_tiles, G.split ? 128 : 256);
   // Small images (the 1/16-scale prior / hyper nets: 75 spatial tiles at 1080p) cannot fill 148 SMs with
   // one N tile: cut Cout into more, narrower N tiles (the activation tile is re-read from L2 instead).
   const int sp1 = cdiv(P.Wo, HTW) * cdiv(P.Ho, HTH) * P.N;
@@ -315,14 +431,14 @@ int vcm_conv_halo_launch(const vcm_conv_desc* d, const ConvParams& P, const void
   G.hw = HTW + P.K - 1;
   G.b_bytes = G.bn * chunk * 2;
   G.b_slot_bytes = round_up(G.b_bytes, 1024);
-  const int slabs = G.ntaps * G.nchunks;
+  const int slabs = G.ntaps * G.nchunks * (G.split ? 3 : 1);
   const int bias_bytes = round_up((G.cout_p < EPI_BIAS_MAX ? G.cout_p : EPI_BIAS_MAX) * 4, 128);
   const int budget = SMEM_LIMIT - 1024 - 512 - bias_bytes - EPI_STAGE_BYTES;   // alignment slack, barriers, bias, staging
   G.scalar_epi = tc_epilogue_mode(d, P);
 
-  auto a_stage = [&](int mh) { return round_up(G.hw * (HTH * mh + P.K - 1) * chunk * 2, 1024); };
+  auto a_stage = [&](int mh) { return (G.split ? 3 : 1) * round_up(G.hw * (HTH * mh + P.K - 1) * chunk * 2, 1024); };
   // resident weights if they leave room for >= 3 activation stages
-  G.resident = (G.n_tiles == 1) && (slabs * G.b_slot_bytes + 3 * a_stage(1) <= budget);
+  G.resident = (G.n_tiles == 1) && (slabs * G.b_slot_bytes + (G.split ? 2 : 3) * a_stage(1) <= budget);
   if (G.resident) {
     G.mh = 1;
     G.b_stages = 0;
@@ -330,9 +446,10 @@ int vcm_conv_halo_launch(const vcm_conv_desc* d, const ConvParams& P, const void
     G.a_stages = (budget - slabs * G.b_slot_bytes) / G.a_stage_bytes;
   } else {
     // 256-pixel items halve the weight traffic per pixel, but only when they still give every SM an item
-    G.mh = (G.bn <= 128 && P.Ho > HTH && cdiv(P.Wo, HTW) * cdiv(P.Ho, 2 * HTH) * P.N * G.n_tiles >= num_sms()) ? 2 : 1;
+    G.mh = (!G.split && G.bn <= 128 && P.Ho > HTH &&
+            cdiv(P.Wo, HTW) * cdiv(P.Ho, 2 * HTH) * P.N * G.n_tiles >= num_sms()) ? 2 : 1;
     G.a_stage_bytes = a_stage(G.mh);
-    G.a_stages = 3;
+    G.a_stages = G.split ? 2 : 3;
     if (G.a_stages * G.a_stage_bytes > budget / 2) G.a_stages = 2;
     if (G.a_stages * G.a_stage_bytes + 2 * G.b_slot_bytes > budget) return 3;
     G.b_stages = (budget - G.a_stages * G.a_stage_bytes) / G.b_slot_bytes;
@@ -350,8 +467,17 @@ int vcm_conv_halo_launch(const vcm_conv_desc* d, const ConvParams& P, const void
   G.tiles_y = cdiv(P.Ho, HTH * G.mh);
   G.num_items = G.tiles_x * G.tiles_y * P.N * G.n_tiles;
   G.nacc = 4 * G.mh * G.bn <= 512 ? 4 : 2;
+  G.a_plane_bytes = G.a_stage_bytes / 3;
+  if (G.split) {
+    // accumulators per item: as many as two items' worth fit the 512 TMEM columns (bn <= 128 -> >= 2),
+    // at most 8, and never more main accumulators than there are main-term slabs
+    G.nsacc = 512 / (2 * G.bn);
+    if (G.nsacc > 8) G.nsacc = 8;
+    if (G.nsacc - 1 > G.ntaps * G.nchunks) G.nsacc = 1 + G.ntaps * G.nchunks;
+    G.nacc = 2;
+  }
   int cols = 32;
-  while (cols < G.nacc * G.mh * G.bn) cols <<= 1;
+  while (cols < G.nacc * (G.split ? G.nsacc : G.mh) * G.bn) cols <<= 1;
   if (cols > 512) return 3;
   G.tmem_cols = cols;
   G.idesc = make_idesc_bf16(128, G.bn);
@@ -359,7 +485,8 @@ int vcm_conv_halo_launch(const vcm_conv_desc* d, const ConvParams& P, const void
 
   CUtensorMap tmA, tmB;
   {
-    cuuint64_t dims[4] = {(cuuint64_t)P.Cin, (cuuint64_t)P.W, (cuuint64_t)P.H, (cuuint64_t)P.N};
+    cuuint64_t dims[4] = {(cuuint64_t)(P.Cin + (G.split ? 2 * G.pstride : 0)), (cuuint64_t)P.W, (cuuint64_t)P.H,
+                          (cuuint64_t)P.N};
     cuuint64_t strides[3] = {(cuuint64_t)P.in_cs * 2, (cuuint64_t)P.W * P.in_cs * 2,
                              (cuuint64_t)P.H * P.W * P.in_cs * 2};
     cuuint32_t box[4] = {(cuuint32_t)chunk, (cuuint32_t)G.hw, (cuuint32_t)G.hh, 1};
@@ -394,15 +521,11 @@ int vcm_conv_halo_launch(const vcm_conv_desc* d, const ConvParams& P, const void
   const int grid = G.num_items < num_sms() ? G.num_items : num_sms();
 #define LAUNCH_HALO(CH)                                                                                  \
   do {                                                                                                   \
-    static bool attr_set = false;                                                                        \
-    if (!attr_set) {                                                                                     \
-      cudaError_t e = cudaFuncSetAttribute(conv_halo_kernel<CH>, cudaFuncAttributeMaxDynamicSharedMemorySize, \
-                                           SMEM_LIMIT);                                                  \
-      if (e != cudaSuccess) {                                                                            \
-        vcm_set_error("vcm_conv_halo_launch: cudaFuncSetAttribute: %s", cudaGetErrorString(e));          \
-        return 1;                                                                                        \
-      }                                                                                                  \
-      attr_set = true;                                                                                   \
+    static bool attr_set[MAX_DEVICES] = {false};                                                         \
+    cudaError_t e = ensure_max_smem(conv_halo_kernel<CH>, attr_set, SMEM_LIMIT);                         \
+    if (e != cudaSuccess) {                                                                              \
+      vcm_set_error("vcm_conv_halo_launch: cudaFuncSetAttribute: %s", cudaGetErrorString(e));            \
+      return 1;                                                                                          \
     }                                                                                                    \
     conv_halo_kernel<CH><<<grid, H_THREADS, smem_bytes, stream>>>(tmA, tmB, P, G);                       \
   } while (0)

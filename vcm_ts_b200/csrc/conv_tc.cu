@@ -34,6 +34,11 @@ constexpr int NUM_THREADS = 384;   // warp 0 TMA, warp 1 MMA + TMEM alloc, warps
 constexpr int MAX_STAGES = 12;
 
 struct TcGeom {
+  // split-bf16 parity mode (VCM_CONV_SPLIT3): a stage holds the three bf16 planes of the activation box
+  // (a_plane bytes apart) and the three weight parts (b_slab bytes apart); the six products x_i*w_j,
+  // i + j <= 2, go to nsacc TMEM accumulators per item ([0] corrections, [1..] main term round-robin over
+  // the stages), which the epilogue adds in fp32 (see conv_halo.cu mma_role_split)
+  int split, pstride, a_plane, b_slab, nsacc;
   int nchunks, ntaps, kiters, stages;
   int a_bytes, b_bytes, b_off, stage_bytes;
   int tiles_x, tiles_y, n_tiles, num_items;   // items = spatial tiles x N tiles
@@ -107,10 +112,19 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           for (int ch = 0; ch < G.nchunks; ++ch) {
             mbar_wait(&empty[stage], phase ^ 1u);
             uint8_t* sa = smem + (size_t)stage * G.stage_bytes;
-            mbar_expect_tx(&full[stage], (uint32_t)(G.a_bytes + G.b_bytes));
-            tma_load_4d(smem_u32(sa), &tmA, &full[stage], ch * CHUNK, cx, cy, n);
-            tma_load_2d(smem_u32(sa + G.b_off), &tmB, &full[stage], 0,
-                        (tap * G.nchunks + ch) * G.cout_p + nt * G.bn);
+            if (G.split) {
+              mbar_expect_tx(&full[stage], 3u * (uint32_t)(G.a_bytes + G.b_bytes));
+              for (int p = 0; p < 3; ++p) {
+                tma_load_4d(smem_u32(sa + p * G.a_plane), &tmA, &full[stage], p * G.pstride + ch * CHUNK, cx, cy, n);
+                tma_load_2d(smem_u32(sa + G.b_off + p * G.b_slab), &tmB, &full[stage], 0,
+                            ((p * G.ntaps + tap) * G.nchunks + ch) * G.cout_p + nt * G.bn);
+              }
+            } else {
+              mbar_expect_tx(&full[stage], (uint32_t)(G.a_bytes + G.b_bytes));
+              tma_load_4d(smem_u32(sa), &tmA, &full[stage], ch * CHUNK, cx, cy, n);
+              tma_load_2d(smem_u32(sa + G.b_off), &tmB, &full[stage], 0,
+                          (tap * G.nchunks + ch) * G.cout_p + nt * G.bn);
+            }
             if (++stage == G.stages) { stage = 0; phase ^= 1u; }
           }
         }
@@ -125,7 +139,9 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     for (int item = blockIdx.x; item < G.num_items; item += gridDim.x) {
       mbar_wait(&tempty[acc], acc_phase ^ 1u);
       tc_fence_after();
-      const uint32_t d_tmem = tmem_base + (uint32_t)(acc * G.bn);
+      const uint32_t d_tmem = tmem_base + (uint32_t)(acc * (G.split ? G.nsacc : 1) * G.bn);
+      uint32_t started = 0;
+      int mctr = 0;
       for (int it = 0; it < G.kiters; ++it) {
         mbar_wait(&full[stage], phase);
         tc_fence_after();
@@ -133,11 +149,31 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           const uint32_t sa = smem_u32(smem + (size_t)stage * G.stage_bytes);
           const uint64_t adesc = make_smem_desc(sa, SBO, LAYOUT);
           const uint64_t bdesc = make_smem_desc(sa + G.b_off, SBO, LAYOUT);
+          if (G.split) {
+            const uint32_t aplane16 = (uint32_t)G.a_plane >> 4, bslab16 = (uint32_t)G.b_slab >> 4;
+            for (int pj = 2; pj >= 0; --pj)
+              for (int pi = 0; pi <= 2 - pj; ++pi) {
+                uint32_t sel = 0;
+                if (pi == 0 && pj == 0) {
+                  sel = 1u + (uint32_t)mctr;
+                  if (++mctr == G.nsacc - 1) mctr = 0;
+                }
+                const uint32_t dd = d_tmem + sel * (uint32_t)G.bn;
+                const uint64_t ad = adesc + (uint64_t)((uint32_t)pi * aplane16);
+                const uint64_t bd = bdesc + (uint64_t)((uint32_t)pj * bslab16);
 #pragma unroll
-          for (int k = 0; k < KSTEPS; ++k) {
-            // advance 16 bf16 = 32 bytes along K inside the swizzle row: +2 in the >>4 address field
-            umma_bf16(d_tmem, adesc + (uint64_t)(2 * k), bdesc + (uint64_t)(2 * k), G.idesc,
-                      (it > 0 || k > 0) ? 1u : 0u);
+                for (int k = 0; k < KSTEPS; ++k)
+                  umma_bf16(dd, ad + (uint64_t)(2 * k), bd + (uint64_t)(2 * k), G.idesc,
+                            k > 0 ? 1u : ((started >> sel) & 1u));
+                started |= 1u << sel;
+              }
+          } else {
+#pragma unroll
+            for (int k = 0; k < KSTEPS; ++k) {
+              // advance 16 bf16 = 32 bytes along K inside the swizzle row: +2 in the >>4 address field
+              umma_bf16(d_tmem, adesc + (uint64_t)(2 * k), bdesc + (uint64_t)(2 * k), G.idesc,
+                        (it > 0 || k > 0) ? 1u : 0u);
+            }
           }
           umma_commit(&empty[stage]);
         }
@@ -163,9 +199,13 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       const int nt = item % G.n_tiles, sp = item / G.n_tiles;
       const int n = sp / sp_tiles, rem = sp - n * sp_tiles;
       const int oy0 = (rem / G.tiles_x) * TH, ox0 = (rem % G.tiles_x) * TW;
-      const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(g * G.bn);
+      const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(g * (G.split ? G.nsacc : 1) * G.bn);
       const int cbase = nt * G.bn;
-      if (G.scalar_epi == 0) {
+      if (G.split) {
+        const int m = q * 32 + lane;
+        epilogue_thread_scalar<float>(P, G.bn, n, oy0 + m / TW, ox0 + m % TW, cbase, taddr, &tfull[g], acc_phase,
+                                      &tempty[g], G.nsacc);
+      } else if (G.scalar_epi == 0) {
         if (G.epi_bw == 32)
           epilogue_warp_vec<32, TW>(P, G.bn, n, oy0, ox0, cbase, taddr, stage, q, lane, &tfull[g], acc_phase, &tempty[g], bias_smem);
         else
@@ -213,6 +253,71 @@ __global__ void pack_umma_kernel(const float* __restrict__ w, __nv_bfloat16* __r
   }
 }
 
+// the same for the three bf16 parts of the fp32 weights: out[part][tap][chunk][Cout_p][CHUNK],
+// w0 = bf16(w), w1 = bf16(w - w0), w2 = bf16(w - w0 - w1) (each difference is exact in fp32)
+__global__ void pack_umma_split3_kernel(const float* __restrict__ w, __nv_bfloat16* __restrict__ out, int Cout,
+                                        int Cout_p, int Cin, int K, int Cin_p, int chunk,
+                                        const int* __restrict__ in_map) {
+  const int nchunks = Cin_p / chunk;
+  const int64_t total = (int64_t)K * K * Cin_p * Cout_p;
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total;
+       i += (int64_t)gridDim.x * blockDim.x) {
+    const int kk = (int)(i % chunk);
+    int64_t r = i / chunk;
+    const int co = (int)(r % Cout_p);
+    r /= Cout_p;
+    const int ch = (int)(r % nchunks);
+    const int tap = (int)(r / nchunks);
+    const int ci_p = ch * chunk + kk;
+    const int ci = in_map ? in_map[ci_p] : ci_p;
+    float v = 0.f;
+    if (co < Cout && ci >= 0 && ci < Cin) v = w[((int64_t)co * Cin + ci) * K * K + tap];
+    const __nv_bfloat16 w0 = __float2bfloat16_rn(v);
+    const float r1 = __fsub_rn(v, __bfloat162float(w0));
+    const __nv_bfloat16 w1 = __float2bfloat16_rn(r1);
+    const __nv_bfloat16 w2 = __float2bfloat16_rn(__fsub_rn(r1, __bfloat162float(w1)));
+    out[i] = w0;
+    out[i + total] = w1;
+    out[i + 2 * total] = w2;
+  }
+}
+
+// fp32 view -> three bf16 planes (vcm_split_bf16x3); one thread = 8 channels of one pixel
+__global__ void split_bf16x3_kernel(const float* __restrict__ src, __nv_bfloat16* __restrict__ dst, int64_t npix,
+                                    int C, int Cp, int src_cs, int dst_cs, int dst_ps, int pre_act, float slope,
+                                    int vec) {
+  const int G8 = Cp / 8;
+  const int64_t total = npix * G8;
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total;
+       i += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t p = i / G8;
+    const int c0 = (int)(i - p * G8) * 8;
+    float v[8];
+    const float* s = src + p * src_cs + c0;
+    if (vec && c0 + 8 <= C) {
+      const float4 a = __ldg(reinterpret_cast<const float4*>(s)), b = __ldg(reinterpret_cast<const float4*>(s + 4));
+      v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w; v[4] = b.x; v[5] = b.y; v[6] = b.z; v[7] = b.w;
+    } else {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) v[j] = c0 + j < C ? __ldg(s + j) : 0.f;
+    }
+    float x0[8], x1[8], x2[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      float x = v[j];
+      if (pre_act) x = leaky(x, slope);
+      x0[j] = __bfloat162float(__float2bfloat16_rn(x));
+      const float r1 = __fsub_rn(x, x0[j]);
+      x1[j] = __bfloat162float(__float2bfloat16_rn(r1));
+      x2[j] = __fsub_rn(r1, x1[j]);
+    }
+    __nv_bfloat16* o = dst + p * dst_cs + c0;
+    *reinterpret_cast<uint4*>(o) = pack8(x0);
+    *reinterpret_cast<uint4*>(o + dst_ps) = pack8(x1);
+    *reinterpret_cast<uint4*>(o + 2 * dst_ps) = pack8(x2);
+  }
+}
+
 // ---------------------------------------------------------------------------------- host
 constexpr int SMEM_BAR_BYTES = 512;
 
@@ -230,6 +335,9 @@ extern "C" int vcm_conv2d_tc_supported(const vcm_conv_desc* d) {
   if ((d->flags & VCM_CONV_POST_ACT) && !(d->post_slope >= 0.f && d->post_slope <= 1.f)) return 0;
   if ((d->flags & VCM_CONV_OUT2) && !(d->out2_slope >= 0.f && d->out2_slope <= 1.f)) return 0;
   if (d->in_cstride % 8) return 0;
+  if ((d->flags & VCM_CONV_SPLIT3) && (d->in_pstride % 8 || d->in_pstride < d->Cin ||
+                                       d->in_cstride < 2 * d->in_pstride + d->Cin || d->out_dtype != VCM_F32))
+    return 0;
   if ((d->flags & VCM_CONV_PIXEL_SHUFFLE) && d->Cout % 4) return 0;
   if (d->stride == 2 && ((d->H & 1) || (d->W & 1))) return 0;
   return 1;
@@ -254,6 +362,35 @@ extern "C" int vcm_pack_conv_weight_umma(const float* w_oihw, void* w_umma, int3
   return 0;
 }
 
+extern "C" int vcm_pack_conv_weight_umma_split3(const float* w_oihw, void* w_umma, int32_t Cout, int32_t Cin,
+                                                int32_t K, int32_t Cin_p, const int32_t* in_map, void* stream) {
+  VCM_CHECK_ARG(w_oihw && w_umma && Cout > 0 && Cin > 0 && K > 0 && Cin_p > 0 && Cin_p % 16 == 0,
+                "bad argument");
+  const int chunk = pick_chunk_split(Cin_p, K);
+  const int cout_p = round_up(Cout, 16);
+  const int64_t total = (int64_t)K * K * Cin_p * cout_p;
+  const int grid = cdiv(total, 256) > 4096 ? 4096 : cdiv(total, 256);
+  pack_umma_split3_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(w_oihw, (__nv_bfloat16*)w_umma, Cout, cout_p,
+                                                                  Cin, K, Cin_p, chunk, in_map);
+  VCM_CHECK_LAUNCH();
+  return 0;
+}
+
+extern "C" int vcm_split_bf16x3(const float* src, void* dst, int64_t npix, int32_t C, int32_t Cp,
+                                int32_t src_cstride, int32_t dst_cstride, int32_t dst_pstride,
+                                int32_t pre_act, float pre_slope, void* stream) {
+  VCM_CHECK_ARG(src && dst && npix > 0 && C > 0 && Cp >= C && Cp % 8 == 0, "bad argument");
+  VCM_CHECK_ARG(dst_cstride % 8 == 0 && dst_pstride % 8 == 0 && ((uintptr_t)dst & 15) == 0,
+                "planes must be 16-byte aligned");
+  const int vec = (src_cstride % 4 == 0 && ((uintptr_t)src & 15) == 0) ? 1 : 0;
+  const int64_t total = npix * (Cp / 8);
+  const int grid = cdiv(total, 256) > 148 * 16 ? 148 * 16 : cdiv(total, 256);
+  split_bf16x3_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(src, (__nv_bfloat16*)dst, npix, C, Cp, src_cstride,
+                                                               dst_cstride, dst_pstride, pre_act, pre_slope, vec);
+  VCM_CHECK_LAUNCH();
+  return 0;
+}
+
 extern "C" int vcm_conv2d_tc_fwd(const vcm_conv_desc* d, const void* x, const void* w_umma,
                                  const float* bias, const void* res, const float* res_scale,
                                  const void* res2, void* y, void* y2, void* stream) {
@@ -269,7 +406,11 @@ extern "C" int vcm_conv2d_tc_fwd(const vcm_conv_desc* d, const void* x, const vo
   VCM_CHECK_ARG(!(P.flags & VCM_CONV_RES_SCALE) || res_scale, "RES_SCALE without scale");
   VCM_CHECK_ARG(!(P.flags & VCM_CONV_RES2) || res2, "RES2 without tensor");
   VCM_CHECK_ARG(!(P.flags & VCM_CONV_OUT2) || y2, "OUT2 without tensor");
-  VCM_CHECK_ARG(((uintptr_t)x & 15) == 0 && ((uintptr_t)w_umma & 15) == 0, "x / weights must be 16-byte aligned");
+  if (((uintptr_t)x & 15) != 0) {   // TMA needs a 16-byte aligned base: the caller falls back to vcm_conv2d_fwd
+    vcm_set_error("vcm_conv2d_tc_fwd: x is not 16-byte aligned (not supported by the tensor-core engine)");
+    return 2;
+  }
+  VCM_CHECK_ARG(((uintptr_t)w_umma & 15) == 0, "weights must be 16-byte aligned");
   P.x = x; P.bias = bias; P.res = res; P.res_scale = res_scale; P.res2 = res2; P.y = y; P.y2 = y2;
 
   // stride-1 shapes go to the halo-tile engine (conv_halo.cu) unless VCM_TC_PERTAP=1 forces this one
@@ -284,15 +425,20 @@ extern "C" int vcm_conv2d_tc_fwd(const vcm_conv_desc* d, const void* x, const vo
 
   TcGeom G;
   memset(&G, 0, sizeof(G));
-  const int chunk = pick_chunk(P.Cin);
-  pick_n_tiling(P.Cout, G.cout_p, G.bn, G.n_tiles);
+  G.split = (P.flags & VCM_CONV_SPLIT3) ? 1 : 0;
+  G.pstride = d->in_pstride;
+  const int chunk = G.split ? pick_chunk_split(P.Cin, P.K) : pick_chunk(P.Cin);
+  pick_n_tiling(P.Cout, G.cout_p, G.bn, G.n_tiles, G.split ? 128 : 256);
   G.nchunks = P.Cin / chunk;
   G.ntaps = P.K * P.K;
   G.kiters = G.ntaps * G.nchunks;
   G.a_bytes = 128 * chunk * 2;
   G.b_bytes = G.bn * chunk * 2;
-  G.b_off = round_up(G.a_bytes, 1024);
-  G.stage_bytes = G.b_off + round_up(G.b_bytes, 1024);
+  G.a_plane = round_up(G.a_bytes, 1024);
+  G.b_slab = round_up(G.b_bytes, 1024);
+  const int nrep = G.split ? 3 : 1;
+  G.b_off = nrep * G.a_plane;
+  G.stage_bytes = G.b_off + nrep * G.b_slab;
   const int bias_bytes = round_up((G.cout_p < EPI_BIAS_MAX ? G.cout_p : EPI_BIAS_MAX) * 4, 128);
   int stages = (SMEM_LIMIT - 1024 - SMEM_BAR_BYTES - bias_bytes - EPI_STAGE_BYTES) / G.stage_bytes;
   if (stages > MAX_STAGES) stages = MAX_STAGES;
@@ -302,8 +448,14 @@ extern "C" int vcm_conv2d_tc_fwd(const vcm_conv_desc* d, const void* x, const vo
   G.tiles_x = cdiv(P.Wo, TW);
   G.tiles_y = cdiv(P.Ho, TH);
   G.num_items = G.tiles_x * G.tiles_y * P.N * G.n_tiles;
+  G.nsacc = 1;
+  if (G.split) {
+    G.nsacc = 512 / (2 * G.bn);
+    if (G.nsacc > 8) G.nsacc = 8;
+    if (G.nsacc - 1 > G.kiters) G.nsacc = 1 + G.kiters;
+  }
   int cols = 32;
-  while (cols < 2 * G.bn) cols <<= 1;
+  while (cols < 2 * G.nsacc * G.bn) cols <<= 1;
   G.tmem_cols = cols;
   G.idesc = make_idesc_bf16(128, G.bn);
   G.scalar_epi = tc_epilogue_mode(d, P);
@@ -314,7 +466,8 @@ extern "C" int vcm_conv2d_tc_fwd(const vcm_conv_desc* d, const void* x, const vo
 
   CUtensorMap tmA, tmB;
   {
-    cuuint64_t dims[4] = {(cuuint64_t)P.Cin, (cuuint64_t)P.W, (cuuint64_t)P.H, (cuuint64_t)P.N};
+    cuuint64_t dims[4] = {(cuuint64_t)(P.Cin + (G.split ? 2 * G.pstride : 0)), (cuuint64_t)P.W, (cuuint64_t)P.H,
+                          (cuuint64_t)P.N};
     cuuint64_t strides[3] = {(cuuint64_t)P.in_cs * 2, (cuuint64_t)P.W * P.in_cs * 2,
                              (cuuint64_t)P.H * P.W * P.in_cs * 2};
     cuuint32_t box[4] = {(cuuint32_t)chunk, (cuuint32_t)(TW * P.stride), (cuuint32_t)(TH * P.stride), 1};
@@ -328,7 +481,7 @@ extern "C" int vcm_conv2d_tc_fwd(const vcm_conv_desc* d, const void* x, const vo
     }
   }
   {
-    cuuint64_t dims[2] = {(cuuint64_t)chunk, (cuuint64_t)G.kiters * G.cout_p};
+    cuuint64_t dims[2] = {(cuuint64_t)chunk, (cuuint64_t)G.kiters * nrep * G.cout_p};
     cuuint64_t strides[1] = {(cuuint64_t)chunk * 2};
     cuuint32_t box[2] = {(cuuint32_t)chunk, (cuuint32_t)G.bn};
     cuuint32_t estr[2] = {1, 1};
@@ -346,15 +499,11 @@ extern "C" int vcm_conv2d_tc_fwd(const vcm_conv_desc* d, const void* x, const vo
   cudaStream_t s = (cudaStream_t)stream;
 #define LAUNCH_TC(CH)                                                                                   \
   do {                                                                                                  \
-    static bool attr_set = false;                                                                       \
-    if (!attr_set) {                                                                                    \
-      cudaError_t e = cudaFuncSetAttribute(conv_tc_kernel<CH>, cudaFuncAttributeMaxDynamicSharedMemorySize, \
-                                           SMEM_LIMIT);                                                 \
-      if (e != cudaSuccess) {                                                                           \
-        vcm_set_error("vcm_conv2d_tc_fwd: cudaFuncSetAttribute: %s", cudaGetErrorString(e));            \
-        return 1;                                                                                       \
-      }                                                                                                 \
-      attr_set = true;                                                                                  \
+    static bool attr_set[MAX_DEVICES] = {false};                                                        \
+    cudaError_t e = ensure_max_smem(conv_tc_kernel<CH>, attr_set, SMEM_LIMIT);                          \
+    if (e != cudaSuccess) {                                                                             \
+      vcm_set_error("vcm_conv2d_tc_fwd: cudaFuncSetAttribute: %s", cudaGetErrorString(e));              \
+      return 1;                                                                                         \
     }                                                                                                   \
     conv_tc_kernel<CH><<<grid, NUM_THREADS, smem_bytes, s>>>(tmA, tmB, P, G);                           \
   } while (0)

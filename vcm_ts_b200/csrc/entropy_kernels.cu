@@ -32,9 +32,12 @@ __device__ __forceinline__ uint8_t scale_index(float sc, float lmin, float lstep
   return (uint8_t)(int)v;
 }
 
-__device__ __forceinline__ int16_t to_sym(float q) {
-  return (int16_t)(int)fminf(fmaxf(q, -32768.f), 32767.f);
-}
+// Symbols travel as int16 (the reference uses int32, entropy_models.py:183-187).  The quantised value
+// itself is clamped to the int16 range BEFORE the reconstruction is formed, so the encoder's y_hat and
+// the decoder's (which only sees the int16 symbol) agree for any input; |q| > 32767 never occurs for a
+// codec operating on [0,1] frames and would cost > 4 kB of bypass digits per symbol in the reference.
+__device__ __forceinline__ float clamp_sym(float q) { return fminf(fmaxf(q, -32768.f), 32767.f); }
+__device__ __forceinline__ int16_t to_sym(float q) { return (int16_t)(int)q; }
 
 template <typename T>
 __global__ void dual_prior_pass0_kernel(const vcm_dp_desc D, const T* __restrict__ y,
@@ -70,7 +73,7 @@ __global__ void dual_prior_pass0_kernel(const vcm_dp_desc D, const T* __restrict
         const float v = __fdiv_rn(ld_as_float(y + pix * D.y_cstride + cc), qs);
         yq[pix * C + cc] = v;
         if (active) {
-          q = rintf(__fsub_rn(v, mu));
+          q = clamp_sym(rintf(__fsub_rn(v, mu)));
           yhat = __fadd_rn(q, mu);
           sym[i] = to_sym(q);
           idx[i] = scale_index(sc, D.log_scale_min, D.log_scale_step);
@@ -122,7 +125,7 @@ __global__ void dual_prior_pass1_kernel(const vcm_dp_desc D, const float* __rest
       float part = 0.f, q = 0.f;
       if (D.mode == 0) {
         if (active) {
-          q = rintf(__fsub_rn(yq[pix * C + cc], mu));
+          q = clamp_sym(rintf(__fsub_rn(yq[pix * C + cc], mu)));
           part = __fadd_rn(q, mu);
           sym[i] = to_sym(q);
           idx[i] = scale_index(sc, D.log_scale_min, D.log_scale_step);
@@ -165,7 +168,7 @@ __global__ void round_latent_kernel(const T* __restrict__ z, T* __restrict__ z_h
     const int c = (int)(r % C);
     const int n = (int)(r / C);
     const int64_t pix = ((int64_t)n * h + hy) * w + wx;
-    const float q = rintf(ld_as_float(z + pix * z_cs + c));
+    const float q = clamp_sym(rintf(ld_as_float(z + pix * z_cs + c)));
     st_from_float(z_hat + pix * zhat_cs + c, q);
     if (sym) sym[i] = to_sym(q);
   }

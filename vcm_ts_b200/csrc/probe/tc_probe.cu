@@ -1,10 +1,22 @@
-// vcm_ts_b200/csrc/tc_probe.cu -- probe of the UMMA shared-memory descriptor semantics (see
+// vcm_ts_b200/csrc/probe/tc_probe.cu (libvcmts_probe.so, diagnostics only) -- probe of the UMMA shared-memory descriptor semantics (see
 // include/vcmts_b200.h vcm_umma_probe): measured on B200, the 128B swizzle is a function of the
 // absolute shared-memory address, so an A tile may start any number of 128-byte rows into a
 // TMA-written buffer and use any multiple of 128 B as the stride between 8-row groups, with
 // base_offset = 0 (profiles/umma_probe_r01.json).  The halo-tile conv variant relies on this.
-#include "tc_ptx.cuh"
+#include <stdarg.h>
+
+#include "../tc_ptx.cuh"
+#include "../../../include/vcmts_b200_probe.h"
 using namespace tc;
+
+// the probe library is self-contained: its own error slot
+void vcm_set_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vfprintf(stderr, fmt, ap);
+  va_end(ap);
+  fputc('\n', stderr);
+}
 
 namespace {
 // ---------------------------------------------------------------------------------- probe
@@ -152,7 +164,7 @@ extern "C" int vcm_umma_rate2(int32_t N, int32_t iters, int32_t start_row, int32
 // `stages`-deep shared-memory ring, walking the image like the conv engines do (CTA-interleaved
 // tiles).  nsplit > 1 issues each box as nsplit TMA operations of bh/nsplit rows.  out[0] = cycles of
 // CTA 0, out[1] = boxes it loaded.
-#include "tc_host.cuh"
+#include "../tc_host.cuh"
 namespace {
 __global__ void __launch_bounds__(64, 1)
 tma_probe_kernel(const __grid_constant__ CUtensorMap tm, int bw, int bh, int tiles_x, int n_tiles, int stages,
@@ -211,6 +223,67 @@ extern "C" int vcm_tma_probe(const void* img, int32_t H, int32_t W, int32_t bw, 
   const int tiles_x = W / bw, n_tiles = tiles_x * (H / bh);
   tma_probe_kernel<<<num_sms(), 64, smem_bytes, (cudaStream_t)stream>>>(tm, bw, bh, tiles_x, n_tiles, stages, stage_bytes,
                                                                        nsplit, out);
+  VCM_CHECK_LAUNCH();
+  return 0;
+}
+
+// ---------------------------------------------------------------------------------- accumulator rounding
+namespace {
+__global__ void __launch_bounds__(128, 1) umma_acc_probe_kernel(const float* __restrict__ a, const float* __restrict__ b,
+                                                                float* __restrict__ out) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  uint8_t* sA = smem;                      // 128 x 128 B
+  uint8_t* sB = smem + 128 * 128;          // 64 x 128 B
+  uint64_t* bar = reinterpret_cast<uint64_t*>(sB + 64 * 128);
+  uint32_t* slot = reinterpret_cast<uint32_t*>(bar + 1);
+  for (int i = threadIdx.x; i < 128 * 64; i += blockDim.x) {
+    const int p = i / 64, c = i % 64;
+    const uint32_t off = p * 128 + (((c >> 3) ^ (p & 7)) << 4) + (c & 7) * 2;
+    *reinterpret_cast<__nv_bfloat16*>(sA + off) = __float2bfloat16_rn(a[i]);
+  }
+  for (int i = threadIdx.x; i < 64 * 64; i += blockDim.x) {
+    const int nrow = i / 64, k = i % 64;
+    const uint32_t off = nrow * 128 + (((k >> 3) ^ (nrow & 7)) << 4) + (k & 7) * 2;
+    *reinterpret_cast<__nv_bfloat16*>(sB + off) = __float2bfloat16_rn(b[k]);
+  }
+  if (threadIdx.x == 0) {
+    mbar_init(bar, 1);
+    fence_barrier_init();
+  }
+  fence_proxy_async();
+  if ((threadIdx.x >> 5) == 0) tmem_alloc(slot, 64);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *slot;
+  if (threadIdx.x == 0) {
+    const uint64_t adesc = make_smem_desc(smem_u32(sA), 1024u, 2u);
+    const uint64_t bdesc = make_smem_desc(smem_u32(sB), 1024u, 2u);
+    const uint32_t idesc = make_idesc_bf16(128, 64);
+#pragma unroll
+    for (int k = 0; k < 4; ++k) umma_bf16(tmem_base, adesc + (uint64_t)(2 * k), bdesc + (uint64_t)(2 * k), idesc, k > 0);
+    umma_commit(bar);
+  }
+  mbar_wait(bar, 0);
+  tc_fence_after();
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  uint32_t r[16];
+  tmem_ld16(tmem_base + ((uint32_t)(warp * 32) << 16), r);
+  out[warp * 32 + lane] = __uint_as_float(r[0]);
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 0) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, 64);
+  }
+}
+}  // namespace
+
+extern "C" int vcm_umma_acc_probe(const float* a, const float* b, float* out, void* stream) {
+  VCM_CHECK_ARG(a && b && out, "null argument");
+  const int smem_bytes = 128 * 128 + 64 * 128 + 64 + 1024;
+  umma_acc_probe_kernel<<<1, 128, smem_bytes, (cudaStream_t)stream>>>(a, b, out);
   VCM_CHECK_LAUNCH();
   return 0;
 }

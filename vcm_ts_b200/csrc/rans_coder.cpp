@@ -104,6 +104,14 @@ extern "C" vcm_cdf_tables* vcm_cdf_tables_new(const int32_t* cdf, const int32_t*
     }
     uint32_t* row = &t->cdf[(size_t)i * stride];
     for (int32_t k = 0; k < stride; ++k) row[k] = (uint32_t)cdf[(size_t)i * stride + k];
+    // the decoder's scan `while (cdf[s + 1] <= cum)` terminates inside the row only if the row spans
+    // [0, 2^16] exactly (ops.cpp:75-79 asserts the same of the tables it builds)
+    if (row[0] != 0u || row[sz - 1] != (1u << kPrecision)) {
+      vcm_set_error("vcm_cdf_tables_new: table %d does not span [0, 65536] (first %u, last %u)", i, row[0],
+                    row[sz - 1]);
+      delete t;
+      return nullptr;
+    }
     int32_t s = 0;
     for (int32_t b = 0; b < 256; ++b) {
       const uint32_t cum = (uint32_t)b << 8;

@@ -279,10 +279,12 @@ __device__ __forceinline__ void epilogue_warp_vec(const ConvParams& P, int bn, i
 
 // ------------------------------------------------------------------------------- scalar path
 // thread = pixel (oy, ox); loops over the bn columns of the slab
+// nsum > 1 (split-bf16 parity mode): the item owns nsum accumulators of bn columns each ([0] = correction
+// terms, [1..] = partial sums of the main term); they are added smallest first with fp32 RN adds.
 template <class T>
 __device__ __forceinline__ void epilogue_thread_scalar(const ConvParams& P, int bn, int n, int oy, int ox,
                                                        int cbase, uint32_t taddr, uint64_t* wait,
-                                                       uint32_t parity, uint64_t* release) {
+                                                       uint32_t parity, uint64_t* release, int nsum = 1) {
   const bool valid = oy < P.Ho && ox < P.Wo;
   if (wait) {
     mbar_wait(wait, parity);
@@ -291,6 +293,12 @@ __device__ __forceinline__ void epilogue_thread_scalar(const ConvParams& P, int 
   for (int cb = 0; cb < bn; cb += 16) {
     float v[16];
     tmem_load_block<16>(taddr + (uint32_t)cb, v);
+    for (int a = 1; a < nsum; ++a) {
+      float u[16];
+      tmem_load_block<16>(taddr + (uint32_t)(a * bn + cb), u);
+#pragma unroll
+      for (int i = 0; i < 16; ++i) v[i] = __fadd_rn(v[i], u[i]);
+    }
     if (cb + 16 >= bn && release) {   // one arrival per warp
       tc_fence_before();
       __syncwarp();

@@ -28,28 +28,50 @@ inline EncodeTiledFn get_encode_fn() {
 }
 
 inline int pick_chunk(int cin) { return cin % 64 == 0 ? 64 : (cin % 32 == 0 ? 32 : 16); }
+// split-bf16 parity mode: a stage holds three planes, so 7x7 halo tiles use 32-channel chunks at most
+inline int pick_chunk_split(int cin, int K) {
+  const int c = pick_chunk(cin);
+  return (K == 7 && c > 32) ? 32 : c;
+}
 inline CUtensorMapSwizzle swizzle_of(int chunk) {
   return chunk == 64 ? CU_TENSOR_MAP_SWIZZLE_128B : (chunk == 32 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_32B);
 }
 inline int round_up(int v, int m) { return (v + m - 1) / m * m; }
 
 // N tiling: Cout padded to 16; above 256 split into the fewest equal tiles that are multiples of 16
-inline void pick_n_tiling(int cout, int& cout_p, int& bn, int& n_tiles) {
+inline void pick_n_tiling(int cout, int& cout_p, int& bn, int& n_tiles, int max_bn = 256) {
   cout_p = round_up(cout, 16);
   n_tiles = 1;
-  while (cout_p / n_tiles > 256 || cout_p % n_tiles || (cout_p / n_tiles) % 16) ++n_tiles;
+  while (cout_p / n_tiles > max_bn || cout_p % n_tiles || (cout_p / n_tiles) % 16) ++n_tiles;
   bn = cout_p / n_tiles;
 }
 
+// per-device state (a process may drive several GPUs; writes are idempotent, so unsynchronised
+// updates from the worker threads are harmless)
+constexpr int MAX_DEVICES = 64;
+inline int current_device() {
+  int dev = 0;
+  cudaGetDevice(&dev);
+  return dev >= 0 && dev < MAX_DEVICES ? dev : 0;
+}
 inline int num_sms() {
-  static int n = 0;
-  if (!n) {
-    int dev = 0;
-    cudaGetDevice(&dev);
-    cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
-    if (n <= 0) n = 148;
+  static int n[MAX_DEVICES] = {0};
+  const int dev = current_device();
+  if (!n[dev]) {
+    int v = 0;
+    cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, dev);
+    n[dev] = v > 0 ? v : 148;
   }
-  return n;
+  return n[dev];
+}
+// cudaFuncAttributeMaxDynamicSharedMemorySize is a per-device attribute of the function
+template <class Kernel>
+inline cudaError_t ensure_max_smem(Kernel k, bool (&done)[MAX_DEVICES], int bytes) {
+  const int dev = current_device();
+  if (done[dev]) return cudaSuccess;
+  const cudaError_t e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+  if (e == cudaSuccess) done[dev] = true;
+  return e;
 }
 
 constexpr int SMEM_LIMIT = 227 * 1024;

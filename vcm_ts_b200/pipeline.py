@@ -81,6 +81,8 @@ class GopPipeline:
                     q_blob.put((t, pack_p(self.enc_dmc.encode_symbols(host), mvq_i, yq_i)))
             except BaseException as e:   # noqa: BLE001
                 errs.append(e)
+                while q_sym.get() is not None:    # drain so the encoder thread can finish (bounded queue)
+                    pass
             finally:
                 q_blob.put(None)
 
