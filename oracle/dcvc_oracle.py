@@ -178,8 +178,8 @@ def lower_bound(x, b):                                # video_net.py:14-21
 
 def torch_warp(feature, flow):                        # video_net.py:32-50
     N, _, H, W = flow.size()
-    hor = torch.linspace(-1.0, 1.0, W, dtype=feature.dtype).view(1, 1, 1, W).expand(N, -1, H, -1)
-    ver = torch.linspace(-1.0, 1.0, H, dtype=feature.dtype).view(1, 1, H, 1).expand(N, -1, -1, W)
+    hor = torch.linspace(-1.0, 1.0, W, dtype=feature.dtype, device=feature.device).view(1, 1, 1, W).expand(N, -1, H, -1)
+    ver = torch.linspace(-1.0, 1.0, H, dtype=feature.dtype, device=feature.device).view(1, 1, H, 1).expand(N, -1, -1, W)
     grid0 = torch.cat([hor, ver], 1)
     flow = torch.cat([flow[:, 0:1] / ((feature.size(3) - 1.0) / 2.0),
                       flow[:, 1:2] / ((feature.size(2) - 1.0) / 2.0)], 1)

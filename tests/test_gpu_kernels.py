@@ -436,7 +436,9 @@ def _dp_inputs(C, h, w, seed):
     return y, q_step, scales, means, prior, q_outer
 
 
-@pytest.mark.parametrize("dist,C,h,w", [("laplace", 64, 18, 30), ("laplace", 96, 12, 20), ("gaussian", 192, 8, 14)])
+@pytest.mark.parametrize("dist,C,h,w", [("laplace", 64, 18, 30), ("laplace", 96, 12, 20), ("gaussian", 192, 8, 14),
+                                        # BASELINE shapes: 1080p latents are 68 x 120
+                                        ("laplace", 64, 68, 120), ("laplace", 96, 68, 120), ("gaussian", 192, 68, 120)])
 def test_dual_prior_kernels_bit_exact(B32, dist, C, h, w):
     """Teacher-forced: identical float inputs -> symbols, scale indexes and y_hat must equal
     common_model.py:104-217 exactly (oracle restatement), encode and decode sides."""
@@ -592,3 +594,96 @@ def test_frame_io_bit_exact_vs_reference_formulas():
         frame_io.frames_to_u8(torch.from_numpy(f).cuda(), H, W, out=host)
         torch.cuda.synchronize()
         assert np.array_equal(host.numpy(), want_u8)
+
+
+# ------------------------------------------------------------------------------------------------------------
+# BASELINE shapes (padded 1080p = 1088 x 1920): tile-edge / 64-bit-index / N-tiling bugs live here, not at 64 x 96
+# ------------------------------------------------------------------------------------------------------------
+FULL_CASES = [
+    # K, stride, Cin, Cout, post, res   (the shapes that carry the FLOPs)
+    (3, 1, 64, 64, 0.01, True),
+    (3, 1, 128, 64, None, False),
+    (7, 1, 32, 64, 0.0, False),
+    (3, 2, 67, 64, 0.1, False),
+]
+
+
+@pytest.mark.parametrize("case", FULL_CASES)
+def test_conv_tcgen05_engine_at_1080p(B16, case):
+    """bf16 tcgen05 engine at 1088 x 1920 against cuDNN's fp32 convolution (TF32 off) of the same
+    bf16-rounded operands: only accumulation order and the final bf16 rounding differ."""
+    K, stride, Cin, Cout, post, use_res = case
+    torch.backends.cudnn.allow_tf32 = False
+    dev, bf = "cuda:0", torch.bfloat16
+    H, W = 1088, 1920
+    g = torch.Generator(device="cpu").manual_seed(900 + FULL_CASES.index(case))
+    x = torch.randn((1, Cin, H, W), generator=g).to(dev).to(bf)
+    w = (torch.randn((Cout, Cin, K, K), generator=g) / (Cin * K * K) ** 0.5).to(dev)
+    b = torch.randn((Cout,), generator=g).to(dev)
+    Ho, Wo = H // stride, W // stride
+    res = torch.randn((1, Cout, Ho, Wo), generator=g).to(dev).to(bf) if use_res else None
+    cin_p = (Cin + 15) // 16 * 16
+    in_map = list(range(Cin)) + [-1] * (cin_p - Cin) if cin_p != Cin else None
+    pc = B16.pack_conv(w, b, in_map=in_map)
+    assert pc.w_umma is not None
+    xv = view_of(x.float(), dtype=bf, cs=cin_p)
+    xv = type(xv)(xv.t, 0, cin_p)
+    out = B16.conv(xv, pc, stride=stride, post=post, res=view_of(res.float(), dtype=bf) if use_res else None)
+    torch.cuda.synchronize()
+    want = ref_conv(x.float(), w.to(bf).float(), b, stride, None, post, False, res.float() if use_res else None,
+                    None, None)
+    got = nchw(out)
+    err = (got - want).abs()
+    tol = 0.01 * want.abs() + 0.02
+    bad = int((err > tol).sum())
+    assert bad == 0, f"{bad} of {err.numel()} outputs off; max err {err.max().item():.4f}"
+
+
+@pytest.mark.parametrize("case", FULL_CASES[:1] + FULL_CASES[3:])
+def test_conv_parity_engine_at_1080p(BPAR, case):
+    """Split-bf16 tensor-core engine at 1088 x 1920 against cuDNN fp32 (TF32 off): fp32-class agreement."""
+    K, stride, Cin, Cout, post, use_res = case
+    torch.backends.cudnn.allow_tf32 = False
+    dev = "cuda:0"
+    H, W = 1088, 1920
+    g = torch.Generator(device="cpu").manual_seed(950 + FULL_CASES.index(case))
+    x = torch.randn((1, Cin, H, W), generator=g).to(dev)
+    w = (torch.randn((Cout, Cin, K, K), generator=g) / (Cin * K * K) ** 0.5).to(dev)
+    b = torch.randn((Cout,), generator=g).to(dev)
+    res = torch.randn((1, Cout, H // stride, W // stride), generator=g).to(dev) if use_res else None
+    pc = BPAR.pack_conv(w, b)
+    out = BPAR.conv(view_of(x), pc, stride=stride, post=post, res=view_of(res) if use_res else None)
+    torch.cuda.synchronize()
+    want = ref_conv(x, w, b, stride, None, post, False, res, None, None)
+    err = (nchw(out) - want).abs().max().item()
+    assert err <= 2e-5, err            # |y| ~ 1..6: a few fp32 ulps of either summation order
+
+
+def test_flow_warp_config3_shapes(B32, B16):
+    """BASELINE config 3: flow_warp at B = 8, 1920 x 1088 (64-channel features in fp32 and bf16, 3-channel
+    frames) against the oracle's torch_warp (video_net.py:32-50) evaluated by ATen on the same device
+    tensors -- including flows that leave the image (border clamp)."""
+    from oracle import dcvc_oracle as O
+    dev = "cuda:0"
+    N, H, W = 8, 1088, 1920
+    g = torch.Generator().manual_seed(31)
+    flow = (torch.randn((N, 2, H // 8, W // 8), generator=g) * 6).to(dev)
+    flow = F.interpolate(flow, size=(H, W), mode="bilinear", align_corners=False).contiguous()
+    flow[:, :, :16] *= 30
+    flow[:, :, :, -16:] *= 30
+    fv = view_of(flow)
+    # fp32 tolerance: sample coordinates reach ~2000 px here (ulp 1.2e-4 px) and ATen works in normalised
+    # coordinates, so a few ulps of coordinate noise times the feature gradient (<= ~2 per pixel for these
+    # 4x-upsampled random features) is the reference's own rounding noise; the 64 x 96 test uses 2e-4.
+    for C, dt, B, atol in ((3, torch.float32, B32, 1e-3), (64, torch.float32, B32, 1e-3),
+                           (64, torch.bfloat16, B16, 2e-2)):
+        feat = F.interpolate(torch.randn((N, C, H // 4, W // 4), generator=g).to(dev), size=(H, W), mode="bilinear",
+                             align_corners=False).contiguous()
+        if dt == torch.bfloat16:
+            feat = feat.bfloat16().float()
+        want = O.torch_warp(feat, flow)
+        got = B.warp(view_of(feat, dtype=dt, cs=C + (8 if C > 3 else 5)), fv)
+        diff = (nchw(got) - (want if dt == torch.float32 else want.bfloat16().float())).abs().max().item()
+        assert diff <= atol, (C, dt, diff)
+        del feat, want, got
+        torch.cuda.empty_cache()
