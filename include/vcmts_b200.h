@@ -164,6 +164,22 @@ int vcm_flow_warp(const void* feat, const float* flow, void* out, int32_t N, int
                   int32_t W, int32_t C, int32_t feat_cstride, int32_t flow_cstride,
                   int32_t out_cstride, int32_t dtype, void* stream);
 
+/* ---- training path: backward kernels ------------------------------------
+ * The reference trains DMC through torch autograd (core/model/dcvc_hem.py:254-322, loss.backward() in
+ * core/engine/train_multi.py:203-268).  Behind this ABI: the weight gradient of a convolution
+ *   dW[co][ci][ky][kx] = sum_pixels dY[pix][co] * X[pix*stride + tap - pad][ci]      (OIHW fp32 out)
+ * with x described by d (in_*) and dy = the gradient of the conv output [N,Ho,Wo] (out_dtype, out_cstride);
+ * `scratch`: vcm_conv2d_wgrad_scratch_floats(d) floats (split partial sums, reduced in fixed order);
+ * and the backward of flow_warp (video_net.py:32-55): gfeat fp32 dense [N,H,W,C] and gflow fp32 dense
+ * [N,H,W,2], both ZERO-INITIALISED by the caller (taps accumulate atomically).  The data gradient of a
+ * convolution is vcm_conv2d_*_fwd on flipped, transposed weights (vcm_ts_b200/training.py).             */
+int64_t vcm_conv2d_wgrad_scratch_floats(const vcm_conv_desc* d);
+int vcm_conv2d_wgrad(const vcm_conv_desc* d, const void* x, const void* dy, float* dw_oihw,
+                     float* scratch, void* stream);
+int vcm_flow_warp_bwd(const void* feat, const float* flow, const void* gout, float* gfeat, float* gflow,
+                      int32_t N, int32_t H, int32_t W, int32_t C, int32_t feat_cstride,
+                      int32_t flow_cstride, int32_t gout_cstride, int32_t dtype, void* stream);
+
 /* ---- entropy-parameter / quantise / likelihood epilogues -------------------------------
  * common_model.py:91-217 (process_with_mask, forward/compress/decompress_dual_prior),
  * entropy_models.py:264-268 (build_indexes).  One fused kernel per checkerboard pass.

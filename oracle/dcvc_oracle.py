@@ -172,8 +172,26 @@ def conv(P, name, x, stride=1):
     return F.conv2d(x, w, P[name + ".bias"], stride, w.shape[-1] // 2)
 
 
-def lower_bound(x, b):                                # video_net.py:14-21
-    return torch.max(x, torch.ones_like(x) * b)
+class LowerBoundFn(torch.autograd.Function):          # video_net.py:14-28 (forward AND its custom backward)
+    @staticmethod
+    def forward(ctx, inputs, bound):
+        b = torch.ones_like(inputs) * bound
+        ctx.save_for_backward(inputs, b)
+        return torch.max(inputs, b)
+
+    @staticmethod
+    def backward(ctx, grad_output):
+        inputs, b = ctx.saved_tensors
+        pass_through = (inputs >= b) | (grad_output < 0)
+        return pass_through.type(grad_output.dtype) * grad_output, None
+
+
+def lower_bound(x, b):                                # LowerBound.apply (same forward value as torch.max)
+    return LowerBoundFn.apply(x, b)
+
+
+def quant_ste(x):                                     # common_model.py:38-44 (training branch)
+    return x + (torch.round(x) - x).clone().detach()
 
 
 def torch_warp(feature, flow):                        # video_net.py:32-50
@@ -463,16 +481,16 @@ def checkerboard(height, width):                      # common_model.py:82-89
     return m0, torch.ones_like(m0) - m0
 
 
-def _masked(y, scales, means, mask):                  # common_model.py:91-102 (eval: round)
+def _masked(y, scales, means, mask, ste=False):       # common_model.py:91-102 (eval: round; train: STE)
     scales_hat = scales * mask
     means_hat = means * mask
     y_res = (y - means_hat) * mask
-    y_q = torch.round(y_res)
+    y_q = quant_ste(y_res) if ste else torch.round(y_res)
     y_hat = y_q + means_hat
     return y_res, y_q, y_hat, scales_hat
 
 
-def dual_prior_forward(P, y, means, scales, quant_step, prior_pre, write=False):
+def dual_prior_forward(P, y, means, scales, quant_step, prior_pre, write=False, ste=False):
     """common_model.py:104-177."""
     _, _, H, W = y.size()
     m0, m1 = checkerboard(H, W)
@@ -481,12 +499,12 @@ def dual_prior_forward(P, y, means, scales, quant_step, prior_pre, write=False):
     y_0, y_1 = y.chunk(2, 1)
     s0, s1 = scales.chunk(2, 1)
     u0, u1 = means.chunk(2, 1)
-    r00, q00, h00, sh00 = _masked(y_0, s0, u0, m0)
-    r11, q11, h11, sh11 = _masked(y_1, s1, u1, m1)
+    r00, q00, h00, sh00 = _masked(y_0, s0, u0, m0, ste)
+    r11, q11, h11, sh11 = _masked(y_1, s1, u1, m1, ste)
     params = torch.cat((h00, h11, means, scales, quant_step), dim=1)
     s0, u0, s1, u1 = three_convs(P, prior_pre, params).chunk(4, 1)
-    r01, q01, h01, sh01 = _masked(y_0, s0, u0, m1)
-    r10, q10, h10, sh10 = _masked(y_1, s1, u1, m0)
+    r01, q01, h01, sh01 = _masked(y_0, s0, u0, m1, ste)
+    r10, q10, h10, sh10 = _masked(y_1, s1, u1, m0, ste)
     y_res = torch.cat((r00 + r01, r11 + r10), dim=1)
     y_q = torch.cat((q00 + q01, q11 + q10), dim=1)
     y_hat = torch.cat((h00 + h01, h11 + h10), dim=1)
@@ -610,32 +628,33 @@ class OracleDMC:
         return conv(P, n + ".4", t, 2)
 
     # -- encoder-side shared trunk --------------------------------------------------
-    def _analyse(self, x, dpb, mv_y_q_scale, y_q_scale, write):
+    def _analyse(self, x, dpb, mv_y_q_scale, y_q_scale, write, ste=False):
         P = self.P
+        rnd = quant_ste if ste else torch.round
         q_mv = self.curr_q("mv_y_q_basic", mv_y_q_scale)
         q_y = self.curr_q("y_q_basic", y_q_scale)
         est_mv = spynet(P, "optic_flow", x, dpb["ref_frame"])
         mv_y = analysis(P, "mv_encoder", est_mv) / q_mv
         mv_z = hyper_analysis(P, "mv_hyper_prior_encoder", mv_y)
-        mv_z_hat = torch.round(mv_z)
+        mv_z_hat = rnd(mv_z)
         mv_params = hyper_synthesis(P, "mv_hyper_prior_decoder", mv_z_hat)
         ref_mv_y = dpb["ref_mv_y"] if dpb["ref_mv_y"] is not None else torch.zeros_like(mv_y)
         mv_q_step, mv_scales, mv_means = three_convs(
             P, "mv_y_prior_fusion", torch.cat((mv_params, ref_mv_y), dim=1)).chunk(3, 1)
         mv_dp = dual_prior_forward(P, mv_y, mv_means, mv_scales, mv_q_step,
-                                   "mv_y_spatial_prior", write)
+                                   "mv_y_spatial_prior", write, ste)
         mv_y_hat = mv_dp[4 if write else 2] * q_mv
         mv_hat = synthesis(P, "mv_decoder", mv_y_hat)
         c1, c2, c3, warp_frame = self.motion_compensation(dpb, mv_hat)
         y = self.contextual_encoder(x, c1, c2, c3) / q_y
         z = self.ctx_hyper_enc(y)
-        z_hat = torch.round(z)
+        z_hat = rnd(z)
         hier = hyper_synthesis(P, "contextual_hyper_prior_decoder", z_hat)
         temporal = self.temporal_prior(c3)
         ref_y = dpb["ref_y"] if dpb["ref_y"] is not None else torch.zeros_like(y)
         q_step, scales, means = three_convs(
             P, "y_prior_fusion", torch.cat((temporal, hier, ref_y), dim=1)).chunk(3, 1)
-        y_dp = dual_prior_forward(P, y, means, scales, q_step, "y_spatial_prior", write)
+        y_dp = dual_prior_forward(P, y, means, scales, q_step, "y_spatial_prior", write, ste)
         y_hat = y_dp[4 if write else 2] * q_y
         feat_res = self.contextual_decoder(y_hat, c2, c3)
         feature, x_hat = self.recon_generation(feat_res, c1)
@@ -741,9 +760,23 @@ class OracleDMC:
     @torch.no_grad()
     def forward_one_frame(self, x, dpb, mv_y_q_scale, y_q_scale):
         """video_model.py:470-592 (eval mode)."""
-        t = self._analyse(x, dpb, mv_y_q_scale, y_q_scale, write=False)
-        _, mv_y_q, _, mv_scales_hat = t["mv_dp"]
-        _, y_q, _, scales_hat = t["y_dp"]
+        return self._forward_one_frame(x, dpb, mv_y_q_scale, y_q_scale, None)
+
+    def forward_one_frame_train(self, x, dpb, mv_y_q_scale, y_q_scale, noise):
+        """video_model.py:470-592 in TRAIN mode, differentiable (P entries may require grad): quant is
+        the straight-through estimator (common_model.py:38-44) and the rates come from
+        add_noise(y_res), add_noise(mv_y_res), add_noise(z), add_noise(mv_z) (:546-550).  `noise`: the four
+        U(-0.5, 0.5) tensors in that order (the reference draws them from the global RNG in this order)."""
+        return self._forward_one_frame(x, dpb, mv_y_q_scale, y_q_scale, noise)
+
+    def _forward_one_frame(self, x, dpb, mv_y_q_scale, y_q_scale, noise):
+        t = self._analyse(x, dpb, mv_y_q_scale, y_q_scale, write=False, ste=noise is not None)
+        mv_y_res, mv_y_q, _, mv_scales_hat = t["mv_dp"]
+        y_res, y_q, _, scales_hat = t["y_dp"]
+        if noise is not None:
+            y_q, mv_y_q = y_res + noise[0], mv_y_res + noise[1]
+            t = dict(t, z_hat=t["z"] + noise[2], mv_z_hat=t["mv_z"] + noise[3], z_hat_q=t["z_hat"],
+                     mv_z_hat_q=t["mv_z_hat"])
         B, _, H, W = x.size()
         pixel_num = H * W
         mse = torch.sum(F.mse_loss(x, t["x_hat"], reduction="none"), dim=(1, 2, 3)) / pixel_num

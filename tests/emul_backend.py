@@ -160,6 +160,28 @@ class EmulBackend:
         self._store(out, y)
         return out
 
+    # ---- training path: contracts of vcm_conv2d_wgrad / vcm_flow_warp_bwd -------------------------
+    def wgrad(self, x, dy, K, stride, Cin, Cout):
+        with torch.enable_grad():
+            w = torch.zeros((Cout, Cin, K, K), requires_grad=True)
+            y = F.conv2d(self._nchw(x).contiguous(), w, None, stride, K // 2)
+            (gw,) = torch.autograd.grad(y, w, self._nchw(dy).contiguous())
+        return gw
+
+    def warp_bwd(self, feat, flow, gout):
+        with torch.enable_grad():
+            f = self._nchw(feat).detach().requires_grad_(True)
+            fl = self._nchw(flow).detach().requires_grad_(True)
+            N, _, H, W = fl.shape
+            hor = torch.linspace(-1.0, 1.0, W).view(1, 1, 1, W).expand(N, -1, H, -1)
+            ver = torch.linspace(-1.0, 1.0, H).view(1, 1, H, 1).expand(N, -1, -1, W)
+            grid = torch.cat([hor, ver], 1) + torch.cat([fl[:, 0:1] / ((W - 1.0) / 2.0),
+                                                         fl[:, 1:2] / ((H - 1.0) / 2.0)], 1)
+            y = F.grid_sample(f, grid.permute(0, 2, 3, 1), mode="bilinear", padding_mode="border",
+                              align_corners=True)
+            gf, gfl = torch.autograd.grad(y, (f, fl), self._nchw(gout))
+        return gf.permute(0, 2, 3, 1).contiguous(), gfl.permute(0, 2, 3, 1).contiguous()
+
     # ---- entropy epilogues (contract of vcm_dual_prior_pass0/1) ------------------------------
     @staticmethod
     def _index(table, sc):

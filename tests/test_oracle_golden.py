@@ -82,3 +82,48 @@ def test_gop_prefix_bit_exact(models, golden_dir, case):
         else:
             assert np.array_equal(feat[:, ::4, ::8, ::8].numpy(), G[p + "ref_feature_sub"])
         dpb = d
+
+
+def _train_case():
+    """Inputs / noise of tests/golden/train_64x128.npz (oracle/gen_train_golden.py), regenerated."""
+    from oracle import gen_train_golden as T
+    xs, ref = T.train_inputs()
+    noise = [T.train_noise(s, T.noise_shapes()) for s in range(2)]
+    return T, xs, ref, noise
+
+
+def test_oracle_train_mode_matches_reference_autograd(golden_dir):
+    """The oracle's TRAIN-mode restatement (straight-through quantiser, noisy likelihoods, LowerBound's
+    custom backward) against the unmodified reference's own autograd: outputs, loss, the gradient norm of
+    every parameter and a few gradients in full, two chained P-frames with batch = 4 anchors."""
+    import torch
+    from oracle import dcvc_oracle as O
+    from oracle import fixture
+    G = np.load(os.path.join(golden_dir, "train_64x128.npz"))
+    T, xs, ref, noise = _train_case()
+    torch.set_num_threads(4)
+    names = [str(n) for n in G["param_names"]]
+    P = fixture.fixture_state_dict(O.state_shapes("dmc"))
+    for k in names:
+        P[k] = P[k].clone().requires_grad_(True)
+    odmc = O.OracleDMC(P)
+    dpb = {"ref_frame": ref, "ref_feature": None, "ref_y": None, "ref_mv_y": None}
+    for step, x in enumerate(xs):
+        p = f"s{step}_"
+        for k in names:
+            P[k].grad = None
+        out = odmc.forward_one_frame_train(x, dpb, P["mv_y_q_scale"], P["y_q_scale"], noise[step])
+        loss = T.loss_of(out)
+        loss.backward()
+        np.testing.assert_allclose(loss.item(), G[p + "loss"][0], rtol=1e-5)
+        for k in ("bpp_mv_y", "bpp_mv_z", "bpp_y", "bpp_z", "bpp", "mse", "me_mse"):
+            np.testing.assert_allclose(out[k].detach().numpy(), G[p + k], rtol=1e-5, err_msg=k)
+        norms = np.array([0.0 if P[k].grad is None else P[k].grad.double().norm().item() for k in names])
+        none = np.array([P[k].grad is None for k in names])
+        assert np.array_equal(none, G[p + "grad_none"]), [n for n, a, b in zip(names, none, G[p + "grad_none"]) if a != b]
+        np.testing.assert_allclose(norms, G[p + "grad_norms"], rtol=2e-3, atol=1e-7)
+        for key in G.files:
+            if key.startswith(p + "grad:"):
+                g = P[key.split(":", 1)[1]].grad.numpy()
+                np.testing.assert_allclose(g, G[key], rtol=2e-3, atol=1e-6 * np.abs(G[key]).max(), err_msg=key)
+        dpb = {k: v.detach() for k, v in out["dpb"].items()}

@@ -65,6 +65,10 @@ _PROTOS = {
     "vcm_flow_down2": (c_int, [_P, _P, c_int32, c_int32, c_int32, c_int32, c_int32, c_float, _P]),
     "vcm_flow_warp": (c_int, [_P, _P, _P, c_int32, c_int32, c_int32, c_int32, c_int32, c_int32,
                               c_int32, c_int32, _P]),
+    "vcm_conv2d_wgrad_scratch_floats": (c_int64, [POINTER(ConvDesc)]),
+    "vcm_conv2d_wgrad": (c_int, [POINTER(ConvDesc), _P, _P, _P, _P, _P]),
+    "vcm_flow_warp_bwd": (c_int, [_P, _P, _P, _P, _P, c_int32, c_int32, c_int32, c_int32, c_int32, c_int32,
+                                  c_int32, c_int32, _P]),
     "vcm_dual_prior_pass0": (c_int, [POINTER(DpDesc), _P, _P, _P, _P, _P, _P, _P, _P, _P]),
     "vcm_dual_prior_pass1": (c_int, [POINTER(DpDesc), _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P]),
     "vcm_round_latent": (c_int, [_P, _P, _P, c_int32, c_int32, c_int32, c_int32, c_int32, c_int32,

@@ -334,6 +334,31 @@ class CudaBackend:
         self.launches += 1
         return out
 
+    # -- training path: backward kernels (training.py) ----------------------------------------
+    def wgrad(self, x, dy, K, stride, Cin, Cout):
+        """dW (OIHW fp32) of a conv with input view x and output-gradient view dy."""
+        assert x.C == Cin and dy.C == Cout and x.N == dy.N
+        d = ConvDesc(x.N, x.H, x.W, Cin, Cout, K, stride, x.cs, dy.cs, 0, 0, 0, 0, 0.0, 0.0, 0.0,
+                     _code(x.dtype), _code(dy.dtype), 0)
+        n = self.L.vcm_conv2d_wgrad_scratch_floats(ctypes.byref(d))
+        scratch = self.empty((max(int(n), 1),), torch.float32)
+        dw = self.empty((Cout, Cin, K, K), torch.float32)
+        check(self.L.vcm_conv2d_wgrad(ctypes.byref(d), x.ptr, dy.ptr, dw.data_ptr(), scratch.data_ptr(),
+                                      self.stream), "vcm_conv2d_wgrad")
+        self.launches += 2
+        return dw
+
+    def warp_bwd(self, feat, flow, gout):
+        """Backward of warp(): (gfeat fp32 [N,H,W,C], gflow fp32 [N,H,W,2]), dense NHWC tensors."""
+        assert flow.dtype == torch.float32 and flow.C == 2 and gout.dtype == feat.dtype
+        gfeat = torch.zeros((feat.N, feat.H, feat.W, feat.C), dtype=torch.float32, device=self.device)
+        gflow = torch.zeros((feat.N, feat.H, feat.W, 2), dtype=torch.float32, device=self.device)
+        check(self.L.vcm_flow_warp_bwd(feat.ptr, flow.ptr, gout.ptr, gfeat.data_ptr(), gflow.data_ptr(), feat.N,
+                                       feat.H, feat.W, feat.C, feat.cs, flow.cs, gout.cs, _code(feat.dtype),
+                                       self.stream), "vcm_flow_warp_bwd")
+        self.launches += 1
+        return gfeat, gflow
+
     # -- entropy epilogues ------------------------------------------------------------------
     def _dp_desc(self, fusion, C, mode, table, y=None, prior=None, params=None, yhat=None):
         return DpDesc(fusion.N, fusion.H, fusion.W, C, y.cs if y is not None else 0, fusion.cs,

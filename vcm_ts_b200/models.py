@@ -720,11 +720,17 @@ class DMC(CompressionModel):
         }
 
     def forward_one_frame(self, x, dpb, mv_y_q_scale=None, y_q_scale=None):
-        """video_model.py:470-592 (eval mode: quant = round, bits from the likelihood kernels)."""
+        """video_model.py:470-592.  In train() mode under autograd the differentiable graph of training.py
+        runs: straight-through quantiser, noisy likelihoods, gradients to every parameter through the
+        device conv / warp kernels.  In eval() mode (or under torch.no_grad()) the fused inference graph
+        below runs and the result carries no gradients."""
         if self.training and torch.is_grad_enabled():
-            raise NotImplementedError(
-                "vcm_ts_b200.DMC: the training path (autograd through the CUDA kernels, noise "
-                "quantisation) is not built yet; call .eval() / torch.no_grad()")
+            from .training import TrainGraph, default_noise
+            rt = self._runtime()
+            if getattr(rt, "train_graph", None) is None:
+                rt.train_graph = TrainGraph(self, rt)
+            noise = getattr(self, "_noise_fn", None) or default_noise
+            return rt.train_graph.forward_one_frame(x, dpb, mv_y_q_scale, y_q_scale, noise)
         with torch.no_grad():
             rt = self._runtime()
             B = rt.B
