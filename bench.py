@@ -494,8 +494,12 @@ def main():
     bpp = workers[0]["bits"] / float(gop * H * W)
     extras = {}
 
+    train = None
+    if not a.no_extras:
+        train = train_sample(dev, rank, world, local, sd_p)      # every rank takes part (DDP all-reduce)
     if rank == 0 and not a.no_extras:
         extras = run_extras(a, workers, src, my_seq_ids, dev, gop, q, sd_p, sd_i)
+        extras["train_step"] = train
 
     roof = None
     cpu = None
@@ -602,6 +606,59 @@ def roofline_entry(rf, peaks, precision):
         json.dump([{"shape": k, "ms": v[0], "tflops": v[1] / max(v[0], 1e-9) / 1e9, "calls": v[2]}
                    for k, v in top], f, indent=1)
     return roof
+
+
+TRAIN_LAMBDAS = (85.0, 170.0, 380.0, 840.0)
+
+
+def train_sample(dev, rank, world, local, sd_p, steps=6, warm=3):
+    """BASELINE config 5: the `trainer_multi` step on the drop-in DMC -- a [4,7,3,256,256] random batch per rank
+    (4 anchors x 7 frames of 256x256 crops), stage ['1','all','single_multi','rec','all',lr,.,'false'] = one
+    P-frame forward / backward / AdamW step per window, bf16 training precision, DistributedDataParallel over
+    NCCL with bf16 gradient buckets (the path's only collective).  The perceptual detector loss is off
+    (torchvision / ultralytics code outside the hot path; no pretrained weights on the box).  Times `steps`
+    optimizer steps with CUDA events (max over ranks), and the same without the gradient all-reduce
+    (DDP no_sync) to expose the collective's cost."""
+    import torch.distributed as dist
+    from vcm_ts_b200.models import DMC
+    from vcm_ts_b200.trainer import Trainer
+    torch.manual_seed(1000 + rank)
+    dmc = DMC(anchor_num=4, precision="bf16")
+    dmc.load_state_dict(sd_p)
+    dmc = dmc.to(dev)
+    tr = Trainer(dmc, TRAIN_LAMBDAS, lr=1e-5, world_size=world, device_ids=[local] if world > 1 else None)
+    batch = torch.rand((4, 7, 3, 256, 256), device=dev)
+
+    def run(n, sync):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        e0.record()
+        for i in range(n):
+            tr.single_step(batch, batch, t_i=i % 6, p_frames=1, sync=sync)
+        e1.record()
+        torch.cuda.synchronize()
+        ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
+        if world > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        return ms.item() / n
+
+    run(warm, True)
+    l0 = dmc._rt.B.launches
+    ms_sync = run(steps, True)
+    launches = (dmc._rt.B.launches - l0) // steps
+    ms_nosync = run(steps, False) if world > 1 else ms_sync
+    nparam = sum(p.numel() for p in dmc.parameters())
+    res = {"value": world * 4 * 1e3 / ms_sync, "unit": "training frames/s (4 anchors x 256x256 per step per GPU)",
+           "ms_per_step": ms_sync, "ms_per_step_without_allreduce": ms_nosync,
+           "allreduce_ms": max(0.0, ms_sync - ms_nosync), "n_gpus": world, "precision": "bf16",
+           "gradient_bytes_bf16": 2 * nparam, "own_kernel_launches_per_step": launches,
+           "sample": f"{steps} optimizer steps (forward + backward + DDP all-reduce + AdamW) after {warm} warm-up "
+                     "steps on a random [4,7,3,256,256] batch per rank; perceptual loss off"}
+    del tr, dmc
+    torch.cuda.empty_cache()
+    return res
 
 
 def run_extras(a, workers, src, my_seq_ids, dev, gop, q, sd_p, sd_i):

@@ -45,6 +45,13 @@ extern "C" {
                                      products x_i*w_j with i + j <= 2 (smallest first) into the fp32
                                      TMEM accumulator: fp32-class accuracy on tcgen05.               */
 
+#define VCM_CONV_PDL 256          /* tensor-core engine: launch with programmatic dependent launch, i.e. the
+                                     kernel's prologue (TMEM allocation, barrier init, WEIGHT loads) may
+                                     overlap the tail of the previous kernel in the stream; activations,
+                                     residuals and outputs are only touched after the predecessor finished.
+                                     Only set it when the packed weights were written by an EARLIER,
+                                     completed launch (not by the kernel just before this one).           */
+
 typedef struct {
   int32_t N, H, W;        /* input batch / height / width                                   */
   int32_t Cin, Cout;      /* logical channels (Cout before pixel shuffle)                   */

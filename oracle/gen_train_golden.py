@@ -33,6 +33,27 @@ FULL_GRADS = ("mv_y_q_scale", "y_q_scale", "mv_y_q_basic", "y_q_basic", "bit_est
               "feature_adaptor_I.weight")
 
 
+def train_state_dict():
+    """Fixture weights (oracle/fixture.py) with the biases of the four layers that predict the entropy SCALES
+    raised to 1.5.  With plain random weights about half of the predicted scales are negative and the
+    reference clamps them to sigma = 1e-5 (common_model.py:66), where d bits / d y is ~1e5 times steeper than
+    anywhere a trained model operates: single gradient elements then depend on the last ulp of a convolution
+    and no two correct implementations agree on them.  Positive scales keep every term of the training
+    objective smooth, so gradients can be compared tightly."""
+    from oracle.dcvc_oracle import state_shapes
+    P = fixture.fixture_state_dict(state_shapes("dmc"))
+    for pre, C in (("mv_y", 64), ("y", 96)):
+        b = P[f"{pre}_prior_fusion.4.bias"].clone()
+        b[C:2 * C] = 1.5                      # chunk order (q_step, scales, means): video_model.py:293,322
+        P[f"{pre}_prior_fusion.4.bias"] = b
+        b = P[f"{pre}_spatial_prior.4.bias"].clone()
+        h = C // 2
+        b[0:h] = 1.5                          # chunk order (scales_0, means_0, scales_1, means_1): common_model.py:135
+        b[C:C + h] = 1.5
+        P[f"{pre}_spatial_prior.4.bias"] = b
+    return P
+
+
 def train_inputs():
     """(x [2][4,3,64,128], ref_frame [4,3,64,128]): four anchors = four shifted crops of one moving texture."""
     fr = fixture.fixture_frames(PH, PW, N + 2, seed=5)
@@ -60,7 +81,7 @@ def main():
     torch.set_num_threads(4)
     DMC, _, _ = import_reference()
     dmc = DMC(anchor_num=N)
-    fixture.apply_fixture(dmc, seed=0)
+    dmc.load_state_dict(train_state_dict(), strict=True)
     dmc.train()
     xs, ref = train_inputs()
     G = {"lambdas": np.array(LAMBDAS), "noise_seed": np.array(NOISE_SEED)}

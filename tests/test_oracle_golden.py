@@ -103,7 +103,7 @@ def test_oracle_train_mode_matches_reference_autograd(golden_dir):
     T, xs, ref, noise = _train_case()
     torch.set_num_threads(4)
     names = [str(n) for n in G["param_names"]]
-    P = fixture.fixture_state_dict(O.state_shapes("dmc"))
+    P = T.train_state_dict()
     for k in names:
         P[k] = P[k].clone().requires_grad_(True)
     odmc = O.OracleDMC(P)

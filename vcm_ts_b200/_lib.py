@@ -13,7 +13,7 @@ SO = os.path.join(HERE, "libvcmts_b200.so")
 
 F32, BF16 = 0, 1
 CONV_PRE_ACT, CONV_POST_ACT, CONV_PIXEL_SHUFFLE = 1, 2, 4
-CONV_RES, CONV_RES_SCALE, CONV_RES2, CONV_OUT2, CONV_SPLIT3 = 8, 16, 32, 64, 128
+CONV_RES, CONV_RES_SCALE, CONV_RES2, CONV_OUT2, CONV_SPLIT3, CONV_PDL = 8, 16, 32, 64, 128, 256
 
 
 class ConvDesc(Structure):

@@ -54,11 +54,12 @@ def _code(dtype):
 
 class PackedConv:
     """Device-side packed weights of one nn.Conv2d (fp32 [tap][Cin_p][Cout] + optional UMMA bf16)."""
-    __slots__ = ("w", "bias", "K", "Cin", "Cout", "w_umma", "bias_tc", "ps", "cin_tc")
+    __slots__ = ("w", "bias", "K", "Cin", "Cout", "w_umma", "bias_tc", "ps", "cin_tc", "fresh")
 
     def __init__(self, w, bias, K, Cin, Cout, w_umma=None):
         self.w, self.bias, self.K, self.Cin, self.Cout, self.w_umma = w, bias, K, Cin, Cout, w_umma
         self.bias_tc, self.ps, self.cin_tc = bias, False, Cin
+        self.fresh = True      # packed by a kernel that may still be running: first launch without PDL
 
 
 PRECISIONS = ("fp32", "bf16", "parity")
@@ -87,6 +88,12 @@ class CudaBackend:
         self.use_twin = precision == "bf16"
         self.launches = 0          # kernels launched (graph replays add their kernel count)
         self.graph_replays = 0
+        # programmatic dependent launch of the tensor-core convs (VCM_CONV_PDL in include/vcmts_b200.h): the
+        # prologue + weight loads of conv n+1 overlap the tail of conv n.  Opt-in (VCM_B200_PDL=1): measured, it
+        # changes neither the 8-sequence throughput (other streams' kernels already fill the SMs a finishing
+        # conv leaves) nor the single-sequence rate (43.4 / 28.9 frames/s with, 43.9 / 28.9 without).
+        import os
+        self.pdl = os.environ.get("VCM_B200_PDL", "0") == "1"
 
     # -- plumbing -------------------------------------------------------------------------
     @property
@@ -169,6 +176,9 @@ class CudaBackend:
             out = self.new(x.N, oh, ow, oc, dtype=out_dtype)
         assert (out.N, out.H, out.W, out.C) == (x.N, oh, ow, oc), "conv output view mismatch"
         flags = 0
+        if self.pdl and not pc.fresh:
+            flags |= _lib.CONV_PDL
+        pc.fresh = False
         if pre is not None:
             flags |= _lib.CONV_PRE_ACT
         if post is not None:

@@ -268,12 +268,14 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
   const uint32_t bias_smem = smem_u32(smem + G.bias_base);
+  pdl_trigger();   // the next kernel of the stream may start its prologue on SMs this grid has left
 
   if (warp < 4) {
   reg_dec<72>();
   if (warp == 0) {
     // ============================ activation producer: one halo box per (item, chunk) ==========
     if (lane == 0) {
+      pdl_wait();   // activations are the previous kernel's output
       int stage = 0;
       uint32_t phase = 0;
       for (int item = blockIdx.x; item < G.num_items; item += gridDim.x) {
@@ -299,6 +301,7 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   } else if (warp == 2) {
     // ============================ weight producer ==============================================
     if (lane == 0) {
+      if (!(P.flags & VCM_CONV_PDL)) pdl_wait();   // weights possibly packed by the kernel just before this one
       const int nparts = G.split ? 3 : 1;
       if (G.resident) {
         // one barrier per tap (the taps past H_MAX_B - 1 share the last one), in the order the MMA role
@@ -354,6 +357,7 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     const int g = (warp - 4) >> 2;
     const int q = warp & 3;   // TMEM lane quarter this warp may access
     const uint32_t stage = smem_u32(smem + G.epi_base) + (uint32_t)((warp - 4) * EPI_STAGE_FLOATS * 4);
+    pdl_wait();   // residuals / SE scales are read and outputs written only after the predecessor finished
     int local = 0;
     for (int item = blockIdx.x; item < G.num_items; item += gridDim.x, ++local) {
       if ((local & 1) != g) continue;
@@ -527,7 +531,17 @@ int vcm_conv_halo_launch(const vcm_conv_desc* d, const ConvParams& P, const void
       vcm_set_error("vcm_conv_halo_launch: cudaFuncSetAttribute: %s", cudaGetErrorString(e));            \
       return 1;                                                                                          \
     }                                                                                                    \
-    conv_halo_kernel<CH><<<grid, H_THREADS, smem_bytes, stream>>>(tmA, tmB, P, G);                       \
+    cudaLaunchConfig_t cfg = {};                                                                         \
+    cfg.gridDim = dim3(grid);                                                                            \
+    cfg.blockDim = dim3(H_THREADS);                                                                      \
+    cfg.dynamicSmemBytes = smem_bytes;                                                                   \
+    cfg.stream = stream;                                                                                 \
+    cudaLaunchAttribute attr[1];                                                                         \
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;                                     \
+    attr[0].val.programmaticStreamSerializationAllowed = 1;                                              \
+    cfg.attrs = attr;                                                                                    \
+    cfg.numAttrs = (P.flags & VCM_CONV_PDL) ? 1 : 0;                                                     \
+    cudaLaunchKernelEx(&cfg, conv_halo_kernel<CH>, tmA, tmB, P, G);                                      \
   } while (0)
   if (chunk == 64) LAUNCH_HALO(64);
   else if (chunk == 32) LAUNCH_HALO(32);

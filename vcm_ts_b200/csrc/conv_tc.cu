@@ -94,12 +94,14 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
   const uint32_t bias_smem = smem_u32(smem + G.bias_base);
+  pdl_trigger();
 
   if (warp < 4) {
   reg_dec<56>();
   if (warp == 0) {
     // ================================ TMA producer (one thread) ================================
     if (lane == 0) {
+      pdl_wait();   // activations are the previous kernel's output (this producer also loads the weights)
       int stage = 0;
       uint32_t phase = 0;
       for (int item = blockIdx.x; item < G.num_items; item += gridDim.x) {
@@ -192,6 +194,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     const int g = (warp - 4) >> 2;
     const int q = warp & 3;  // TMEM lane quarter this warp may access
     const uint32_t stage = smem_u32(smem + G.epi_base) + (uint32_t)((warp - 4) * EPI_STAGE_FLOATS * 4);
+    pdl_wait();
     uint32_t acc_phase = 0;
     int local = 0;
     for (int item = blockIdx.x; item < G.num_items; item += gridDim.x, ++local) {
@@ -505,7 +508,17 @@ extern "C" int vcm_conv2d_tc_fwd(const vcm_conv_desc* d, const void* x, const vo
       vcm_set_error("vcm_conv2d_tc_fwd: cudaFuncSetAttribute: %s", cudaGetErrorString(e));              \
       return 1;                                                                                         \
     }                                                                                                   \
-    conv_tc_kernel<CH><<<grid, NUM_THREADS, smem_bytes, s>>>(tmA, tmB, P, G);                           \
+    cudaLaunchConfig_t cfg = {};                                                                        \
+    cfg.gridDim = dim3(grid);                                                                           \
+    cfg.blockDim = dim3(NUM_THREADS);                                                                   \
+    cfg.dynamicSmemBytes = smem_bytes;                                                                  \
+    cfg.stream = s;                                                                                     \
+    cudaLaunchAttribute attr[1];                                                                        \
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;                                    \
+    attr[0].val.programmaticStreamSerializationAllowed = 1;                                             \
+    cfg.attrs = attr;                                                                                   \
+    cfg.numAttrs = (P.flags & VCM_CONV_PDL) ? 1 : 0;                                                    \
+    cudaLaunchKernelEx(&cfg, conv_tc_kernel<CH>, tmA, tmB, P, G);                                       \
   } while (0)
   if (chunk == 64) LAUNCH_TC(64);
   else if (chunk == 32) LAUNCH_TC(32);

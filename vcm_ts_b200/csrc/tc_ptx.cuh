@@ -52,6 +52,12 @@ template <int N>
 __device__ __forceinline__ void reg_inc() {
   asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(N));
 }
+// Programmatic dependent launch: a kernel launched with programmaticStreamSerializationAllowed may become
+// resident while its predecessor in the stream is still running; it must not touch anything the predecessor
+// reads or writes before pdl_wait() (which returns once the predecessor grid has completed and flushed).
+// pdl_trigger() lets the successor's CTAs start their prologue as soon as SM resources free up.
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 __device__ __forceinline__ void fence_barrier_init() {
   asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
 }

@@ -68,6 +68,7 @@ class Trainer:
     def __init__(self, dmc, lambdas, lr=1e-4, world_size=1, device_ids=None, bf16_grad_buckets=True,
                  dist_lambda=1.0, pl_lambda=0.0, perceptual_fn=None):
         self.module = DCVCTrainModule(dmc, lambdas, dist_lambda, pl_lambda, perceptual_fn)
+        self.module.to(next(dmc.parameters()).device)
         self.model = self.module
         if world_size > 1:
             from torch.nn.parallel import DistributedDataParallel as DDP
