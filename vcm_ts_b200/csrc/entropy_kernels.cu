@@ -26,8 +26,13 @@ inline int ew_grid(int64_t total) {
 
 __device__ __forceinline__ uint8_t scale_index(float sc, float lmin, float lstep) {
   const float s = fmaxf(sc, 1e-5f);
-  // log through double: the correctly rounded fp32 log, the best match for the reference's CPU logf
-  float v = __fdiv_rn(__fsub_rn((float)log((double)s), lmin), lstep);
+  // The index is floor((ln s - lmin) / step).  logf (<= 1 ulp of |ln s| <= 11.6, i.e. <= 2.8e-5 in the
+  // quotient) decides it unless the quotient lands within 2e-4 of an integer; only then is the correctly rounded fp32 log
+  // taken through double -- the best match for the reference's CPU logf -- which is ~60x slower on B200
+  // (ncu r02: 53 us per pass with the double log on every element, DRAM 1.7 % of peak).
+  float v = __fdiv_rn(__fsub_rn(logf(s), lmin), lstep);
+  const float fr = v - floorf(v);
+  if (fr < 2e-4f || fr > 1.f - 2e-4f) v = __fdiv_rn(__fsub_rn((float)log((double)s), lmin), lstep);
   v = fminf(fmaxf(v, 0.f), 255.f);
   return (uint8_t)(int)v;
 }
