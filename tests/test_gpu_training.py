@@ -33,6 +33,9 @@ WG_CASES = [
     # K, stride, Cin, Cout, H, W, N
     (3, 1, 64, 64, 24, 40, 2), (3, 2, 67, 64, 32, 48, 1), (7, 1, 8, 32, 20, 28, 1), (1, 1, 64, 256, 17, 30, 1),
     (1, 2, 2, 64, 32, 48, 2), (3, 1, 480, 384, 9, 15, 1), (7, 1, 16, 2, 24, 40, 1), (3, 1, 128, 64, 33, 47, 1),
+    # tensor-core path (bf16, Cin % 16 == 0): strides, Cout tails, small and large images
+    (3, 2, 64, 96, 32, 48, 2), (1, 2, 64, 64, 32, 32, 1), (3, 1, 64, 64, 256, 256, 4), (7, 1, 32, 64, 64, 64, 2),
+    (3, 1, 96, 144, 16, 16, 4), (3, 1, 192, 192, 16, 16, 1), (3, 2, 144, 192, 32, 32, 1), (1, 1, 96, 384, 4, 4, 4),
 ]
 
 

@@ -178,3 +178,28 @@ def test_ddp_gloo_two_ranks_average_gradients():
             continue
         want = 0.5 * (singles[0][k] + singles[1][k]).numpy()
         np.testing.assert_allclose(g0[k], want, rtol=1e-4, atol=1e-6 * np.abs(want).max(), err_msg=k)
+
+
+def test_intra_train_mode_gradients_and_eval_consistency():
+    """IntraNoAR.forward in train() mode (image_model.py:54-105): gradients reach every parameter, and with
+    the noise switched off its rate / distortion stay close to the eval-mode (hard rounding) forward of the
+    fused inference graph on the same weights (same graph, same quantised latents; only the rate term sees
+    y_res instead of round(y_res))."""
+    from vcm_ts_b200.models import IntraNoAR
+    torch.set_num_threads(4)
+    intra = IntraNoAR(precision="fp32")
+    intra.load_state_dict(fixture.fixture_state_dict(O.state_shapes("intra")), strict=True)
+    intra._backend_factory = lambda dev, prec: EmulBackend(dev, prec)
+    x = fixture.fixture_frames(64, 128, 2, seed=3)
+    intra.train()
+    intra._noise_fn = lambda t: torch.zeros_like(t)
+    out = intra(x, intra.q_scale[:2])
+    (out["bpp"].sum() + 100.0 * out["mse"].sum()).backward()
+    missing = [k for k, p in intra.named_parameters() if p.grad is None]
+    assert not missing, missing
+    assert all(torch.isfinite(p.grad).all() for p in intra.parameters())
+    intra.eval()
+    ref = intra(x, intra.q_scale[:2].detach())
+    torch.testing.assert_close(out["x_hat"].detach(), ref["x_hat"], rtol=1e-4, atol=1e-4)
+    torch.testing.assert_close(out["mse"].detach(), ref["mse"], rtol=1e-4, atol=1e-6)
+    torch.testing.assert_close(out["bpp_z"].detach(), ref["bpp_z"], rtol=0.2, atol=1e-3)

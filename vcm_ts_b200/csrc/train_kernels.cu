@@ -4,6 +4,8 @@
 // flow_warp (video_net.py:32-55, grid_sample bilinear / border / align_corners=True) are device kernels
 // behind the C-ABI; the data gradient of a convolution is the forward engine run on flipped, transposed
 // weights (vcm_ts_b200/training.py).
+#include <stdlib.h>
+
 #include "common.cuh"
 
 namespace {
@@ -169,8 +171,12 @@ inline int grid_for(int64_t total) {
 
 }  // namespace
 
-extern "C" int64_t vcm_conv2d_wgrad_scratch_floats(const vcm_conv_desc* d) {
-  if (!d) return 0;
+// tensor-core path (wgrad_tc.cu)
+int64_t vcm_wgrad_tc_scratch_floats(const vcm_conv_desc* d);
+int vcm_wgrad_tc_launch(const vcm_conv_desc* d, const void* x, const void* dy, float* scratch, int* nsplit_out,
+                        cudaStream_t stream);
+
+static int64_t simt_scratch_floats(const vcm_conv_desc* d) {
   const int pad = d->K / 2;
   const int Ho = (d->H + 2 * pad - d->K) / d->stride + 1, Wo = (d->W + 2 * pad - d->K) / d->stride + 1;
   const int64_t npix = (int64_t)d->N * Ho * Wo;
@@ -180,6 +186,12 @@ extern "C" int64_t vcm_conv2d_wgrad_scratch_floats(const vcm_conv_desc* d) {
   if (nsplit > max_split) nsplit = max_split;
   if (nsplit < 1) nsplit = 1;
   return (int64_t)nsplit * d->K * d->K * d->Cout * d->Cin;
+}
+
+extern "C" int64_t vcm_conv2d_wgrad_scratch_floats(const vcm_conv_desc* d) {
+  if (!d) return 0;
+  const int64_t a = simt_scratch_floats(d), b = vcm_wgrad_tc_scratch_floats(d);
+  return a > b ? a : b;
 }
 
 extern "C" int vcm_conv2d_wgrad(const vcm_conv_desc* d, const void* x, const void* dy, float* dw_oihw,
@@ -192,11 +204,22 @@ extern "C" int vcm_conv2d_wgrad(const vcm_conv_desc* d, const void* x, const voi
   const int taps = d->K * d->K;
   const int tiles_ci = cdiv(d->Cin, WG_T), tiles_co = cdiv(d->Cout, WG_T);
   const int64_t per = (int64_t)taps * d->Cout * d->Cin;
-  const int nsplit = (int)(vcm_conv2d_wgrad_scratch_floats(d) / per);
+  cudaStream_t s = (cudaStream_t)stream;
+  {   // bf16 operands with 16-aligned Cin: implicit GEMM over pixels on tcgen05 (wgrad_tc.cu)
+    static const bool no_tc = getenv("VCM_WGRAD_SIMT") && getenv("VCM_WGRAD_SIMT")[0] == '1';
+    int ns = 0;
+    const int rc = no_tc ? 3 : vcm_wgrad_tc_launch(d, x, dy, scratch, &ns, s);
+    if (rc == 1) return 1;
+    if (rc == 0) {
+      wgrad_reduce_kernel<<<grid_for(per), 256, 0, s>>>(scratch, dw_oihw, ns, taps, d->Cout, d->Cin);
+      VCM_CHECK_LAUNCH();
+      return 0;
+    }
+  }
+  const int nsplit = (int)(simt_scratch_floats(d) / per);
   int64_t pps = (npix + nsplit - 1) / nsplit;
   pps = (pps + WG_PB - 1) / WG_PB * WG_PB;
   dim3 grid(tiles_ci * tiles_co * taps, nsplit);
-  cudaStream_t s = (cudaStream_t)stream;
 #define WG_LAUNCH(TX, TY)                                                                                         \
   wgrad_partial_kernel<TX, TY><<<grid, 256, 0, s>>>((const TX*)x, (const TY*)dy, scratch, d->N, d->H, d->W, Ho, Wo, \
                                                     d->Cin, d->Cout, d->K, d->stride, pad, d->in_cstride,          \

@@ -794,9 +794,15 @@ class IntraNoAR(CompressionModel):
         return g.conv("refine.1", g.unet("refine.0", t), out_dtype=F32)
 
     def forward(self, x, q_scale=None):
-        """image_model.py:54-105 (eval mode)."""
+        """image_model.py:54-105.  In train() mode under autograd: the differentiable graph of training.py
+        (straight-through quantiser, noisy likelihoods, gradients through the device conv kernels); otherwise
+        the fused inference graph."""
         if self.training and torch.is_grad_enabled():
-            raise NotImplementedError("vcm_ts_b200.IntraNoAR: training path not built; use eval()/no_grad()")
+            from .training import TrainGraph, default_noise
+            rt = self._runtime()
+            if getattr(rt, "train_graph", None) is None:
+                rt.train_graph = TrainGraph(self, rt)
+            return rt.train_graph.intra_forward(x, q_scale, getattr(self, "_noise_fn", None) or default_noise)
         with torch.no_grad():
             rt = self._runtime()
             B = rt.B

@@ -83,8 +83,21 @@ class ConvFn(torch.autograd.Function):
         if ctx.needs_input_grad[2]:
             gb = gyc.sum(dim=(0, 2, 3), dtype=F32).to(weight.dtype)
         if ctx.needs_input_grad[1]:
-            xv, _ = _view(xc)
-            gw = B.wgrad(xv, gyv, K, stride, Cin, Cout).to(weight.dtype)
+            xw, gyw, cin_w = xc, gyc, Cin
+            if xc.dtype == torch.bfloat16:
+                # the tcgen05 weight-gradient kernel wants bf16 operands and 16-aligned input channels: cast
+                # an fp32 output gradient, zero-pad a 2/3/8/67-channel input (the pad columns are dropped)
+                if gyw.dtype != torch.bfloat16:
+                    gyw = gyw.to(torch.bfloat16)
+                if Cin % 16:
+                    cin_w = (Cin + 15) // 16 * 16
+                    xw = F.pad(xc, (0, 0, 0, 0, 0, cin_w - Cin)).contiguous(memory_format=CL)
+            xv, _ = _view(xw)
+            gwv, _ = _view(gyw)
+            gw = B.wgrad(xv, gwv, K, stride, cin_w, Cout)
+            if cin_w != Cin:
+                gw = gw[:, :Cin]
+            gw = gw.to(weight.dtype)
         if ctx.needs_input_grad[0]:
             pcT = g.packed_dgrad(ctx.name, weight)
             src = gyv
@@ -311,6 +324,11 @@ class TrainGraph:
         d = torch.distributions.laplace.Laplace(torch.zeros_like(sigma), sigma)
         return self.probs_to_bits(d.cdf(y + 0.5) - d.cdf(y - 0.5))
 
+    def gaussian_bits(self, y, sigma):
+        sigma = sigma.clamp(0.11, 1e10)
+        d = torch.distributions.normal.Normal(torch.zeros_like(sigma), sigma)
+        return self.probs_to_bits(d.cdf(y + 0.5) - d.cdf(y - 0.5))
+
     def z_bits(self, z, name):
         def cdf(x):
             for f in ("f1", "f2", "f3", "f4"):
@@ -440,6 +458,33 @@ class TrainGraph:
                 "bit": torch.sum(bpp) * pixel_num, "bit_y": torch.sum(bpp_y) * pixel_num,
                 "bit_z": torch.sum(bpp_z) * pixel_num, "bit_mv_y": torch.sum(bpp_mv_y) * pixel_num,
                 "bit_mv_z": torch.sum(bpp_mv_z) * pixel_num}
+
+
+    # ---- image_model.py:54-105 (IntraNoAR.forward, training branch)
+    def intra_forward(self, x, q_scale, noise_fn):
+        m = self.m
+        x = x.to(F32)
+        curr_q = LowerBoundFn.apply(m.q_basic, 0.5) * q_scale
+        y = self.analysis("enc", x, out_dtype=F32) / curr_q
+        z = self.hyper_analysis("hyper_enc", y)
+        z_hat = self.quant(z)
+        params = self.hyper_synthesis("hyper_dec", z_hat)
+        q_step, scales, means = self.three_convs("y_prior_fusion", params).chunk(3, 1)
+        y_res, y_q, y_hat, scales_hat = self.dual_prior(y, means, scales, q_step, "y_spatial_prior")
+        y_hat = y_hat * curr_q
+        t = self.synthesis("dec", y_hat)
+        x_hat = self.conv("refine.1", self.unet("refine.0", t), out_dtype=F32)
+        if m.training:
+            y_for_bit, z_for_bit = y_res + noise_fn(y_res), z + noise_fn(z)
+        else:
+            y_for_bit, z_for_bit = y_q, z_hat
+        _, _, H, W = x.shape
+        pixel_num = H * W
+        bpp_y = torch.sum(self.gaussian_bits(y_for_bit, scales_hat), dim=(1, 2, 3)) / pixel_num
+        bpp_z = torch.sum(self.z_bits(z_for_bit, "bit_estimator_z"), dim=(1, 2, 3)) / pixel_num
+        mse = torch.sum((x - x_hat) ** 2, dim=(1, 2, 3)) / pixel_num
+        bits = torch.sum(bpp_y + bpp_z) * pixel_num
+        return {"x_hat": x_hat, "mse": mse, "bit": bits.item(), "bpp": bpp_y + bpp_z, "bpp_y": bpp_y, "bpp_z": bpp_z}
 
 
 def default_noise(x):
