@@ -690,6 +690,16 @@ def run_extras(a, workers, src, my_seq_ids, dev, gop, q, sd_p, sd_i):
         for _ in range(2):      # eager pass, then the pass that captures the encoder-chain graphs
             pipe.code_gop(frames[:4], H, W, q, q, q)
         single["pipelined"] = wall_fps(lambda: pipe.code_gop(frames, H, W, q, q, q), n1)
+        # the same ONE sequence when it is long: its GOPs are independent units (every I-frame resets the decoded
+        # picture buffer, video_coder.py:122-130), so S of them are coded concurrently by the S workers
+        sid = my_seq_ids[0]
+
+        def one(w, u):
+            w["bits"], _ = code_gop(w["dmc"], w["intra"], src[sid][1], n1, q)
+        single["gop_interleaved"] = wall_fps(lambda: run_pool(workers, [(sid, g_) for g_ in range(S)], one, dev),
+                                             S * n1)
+        single["note"] = (f"serial / pipelined: one GOP of {n1} frames alone on the GPU; gop_interleaved: {S} GOPs of "
+                          f"{n1} frames of the same sequence in flight")
     out["single_sequence_frames_per_s"] = single
 
     def sample_mode(precision, n_workers, n_frames, sds, label):

@@ -13,7 +13,7 @@ STAGES=${STAGES:-"k_fp32 k_tc k_parity e2e_exact e2e_bf16 train smoke bench"}
 # compute-sanitizer: ONE tool per gpurun call (B200_PROFILING.md), on a handful of small kernel cases that cover
 # the hand-rolled mbarrier / TMEM / TMA pipelines:  STAGES=san_memcheck  /  STAGES=san_racecheck  /  ...
 SAN_TESTS='tests/test_gpu_kernels.py -m gpu -q -x -k "(tcgen05_engine and (case0 or case1 or case12 or case18)) or (parity_engine and (case0 or case2 or case10)) or dual_prior or motion_kernels or split_bf16x3"'
-SAN_TRAIN='tests/test_gpu_training.py -m gpu -q -x -k "(wgrad_kernel and (case0 or case8 or case11)) or flow_warp_backward"
+SAN_TRAIN='tests/test_gpu_training.py -m gpu -q -x -k "(wgrad_kernel and (case0 or case8 or case11)) or flow_warp_backward"'
 for s in $STAGES; do case $s in
   k_fp32) run k_fp32 150 python -m pytest tests/test_gpu_kernels.py -m gpu -q -k "fp32_engine or mixed or layout or se_layer or motion or dual_prior or round_and_bits or vector_path or frame_io" ;;
   k_probe) run k_probe 100 python -m pytest tests/test_gpu_kernels.py -m gpu -q -s -k "probe" ;;

@@ -687,3 +687,50 @@ def test_flow_warp_config3_shapes(B32, B16):
         assert diff <= atol, (C, dt, diff)
         del feat, want, got
         torch.cuda.empty_cache()
+
+
+def test_kernels_do_not_write_outside_their_outputs(B16, BPAR, B32):
+    """compute-sanitizer is closed on this GPU pool, so out-of-bounds WRITES are caught with guard bands: every
+    output lives inside a larger sentinel-filled allocation (whole guard tensors before / after it, and guard
+    channels left and right of the view inside each pixel); after the kernel all sentinels must be intact.
+    Ragged sizes on purpose (tile tails of the tcgen05 engines, odd channel counts)."""
+    from vcm_ts_b200.backend import View
+    dev = "cuda:0"
+    g = torch.Generator().manual_seed(5)
+    SENT = 12345.0
+
+    def guarded(N, H, W, C, dtype, pad_c=8):
+        big = torch.full((N + 2, H, W, C + 2 * pad_c), SENT, dtype=dtype, device=dev)
+        return big, View(big[1:N + 1], pad_c, C)
+
+    def intact(big, N, C, pad_c=8):
+        s = torch.tensor(SENT, dtype=big.dtype, device=dev)
+        return bool((big[0] == s).all() and (big[N + 1] == s).all() and (big[1:N + 1, ..., :pad_c] == s).all()
+                    and (big[1:N + 1, ..., pad_c + C:] == s).all())
+
+    cases = [(B16, torch.bfloat16, 3, 1, 64, 64, 37, 53), (B16, torch.bfloat16, 3, 2, 64, 96, 38, 54),
+             (B16, torch.bfloat16, 7, 1, 32, 16, 21, 19), (B16, torch.bfloat16, 3, 1, 192, 192, 19, 23),
+             (BPAR, torch.float32, 3, 1, 64, 64, 37, 53), (BPAR, torch.float32, 3, 2, 67, 64, 38, 54),
+             (B32, torch.float32, 3, 1, 67, 3, 21, 19)]
+    for Bk, dt, K, stride, Cin, Cout, H, W in cases:
+        w = (torch.randn((Cout, Cin, K, K), generator=g) / (Cin * K * K) ** 0.5).to(dev)
+        pc = Bk.pack_conv(w, torch.zeros(Cout, device=dev))
+        x = view_of(torch.randn((2, Cin, H, W), generator=g).to(dev), dtype=dt,
+                    cs=(Cin + 15) // 16 * 16 if dt == torch.bfloat16 else Cin)
+        Ho, Wo = (H + 2 * (K // 2) - K) // stride + 1, (W + 2 * (K // 2) - K) // stride + 1
+        big, out = guarded(2, Ho, Wo, Cout, dt)
+        Bk.conv(x, pc, out=out, stride=stride, post=0.1)
+        torch.cuda.synchronize()
+        assert intact(big, 2, Cout), ("conv", Bk.precision, K, stride, Cin, Cout)
+        assert torch.isfinite(out.dense().float()).all() and float(out.dense().float().abs().max()) < 1e3
+    # warp / maxpool / copy into guarded views
+    feat = view_of(torch.randn((2, 64, 37, 53), generator=g).to(dev), dtype=torch.bfloat16)
+    flow = view_of((torch.randn((2, 2, 37, 53), generator=g) * 30).to(dev))
+    big, out = guarded(2, 37, 53, 64, torch.bfloat16)
+    B16.warp(feat, flow, out=out)
+    torch.cuda.synchronize()
+    assert intact(big, 2, 64), "warp"
+    big, out = guarded(2, 18, 26, 64, torch.bfloat16)
+    B16.maxpool(feat, out=out)
+    torch.cuda.synchronize()
+    assert intact(big, 2, 64), "maxpool"

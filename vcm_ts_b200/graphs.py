@@ -38,7 +38,7 @@ def drive_eager(gen, service, device):
     try:
         while True:
             req = gen.send(reply)
-            reply = service(req).to(device)
+            reply = service(req).to(device, non_blocking=True)
     except StopIteration as e:
         return e.value
 
@@ -66,7 +66,7 @@ class Program:
             B.launches += n
             B.graph_replays += 1
             if req is not None:
-                up.copy_(service(req))
+                up.copy_(service(req), non_blocking=True)    # pinned host buffer (models._Staging)
         return self.result
 
 

@@ -35,11 +35,49 @@ class _Node(nn.Module):
     """Anonymous container so parameter names match the reference's module tree."""
 
 
+class _Staging:
+    """Pinned host buffers for the symbol / scale-index hand-off with the host entropy coder
+    (entropy_models.py:183-195, 270-281 move int32 tensors with blocking pageable copies).  Device -> host:
+    every tensor of a hand-off is copied asynchronously into its pinned buffer and ONE event is waited for;
+    host -> device copies of decoded symbols are asynchronous from pinned memory (the next launch on the
+    stream orders after them).  Buffers are reused round-robin (`depth` generations per tag), so a consumer
+    on another thread (pipeline.py) may hold the previous generations while the next frame is staged."""
+
+    def __init__(self, device, depth=4):
+        self.device, self.depth = device, depth
+        self.bufs, self.gen = {}, {}
+        self.pin = device.type == "cuda"
+
+    def _buf(self, key, shape, dtype):
+        b = self.bufs.get(key)
+        if b is None:
+            b = torch.empty(shape, dtype=dtype, pin_memory=self.pin)
+            self.bufs[key] = b
+        return b
+
+    def to_host(self, tag, *tensors):
+        g = self.gen[tag] = (self.gen.get(tag, -1) + 1) % self.depth
+        outs = []
+        for i, t in enumerate(tensors):
+            b = self._buf((tag, g, i, tuple(t.shape), t.dtype), tuple(t.shape), t.dtype)
+            b.copy_(t, non_blocking=True)
+            outs.append(b)
+        if self.pin:
+            ev = torch.cuda.Event()
+            ev.record(torch.cuda.current_stream(self.device))
+            ev.synchronize()
+        return outs
+
+    def host_buf(self, tag, shape, dtype):
+        return self._buf((tag, tuple(shape), dtype), tuple(shape), dtype)
+
+
 class _Runtime:
     """Per-process, per-device state that must not be pickled: backend, packed weights, coder."""
 
     def __init__(self, backend):
         self.B = backend
+        self.staging = _Staging(backend.device)
         self.packed = {}
         self.lin = {}
         self.persist = {}
@@ -269,22 +307,21 @@ class CompressionModel(nn.Module):
         return B.from_nchw(entry, out=out)
 
     # ---- host <-> device symbol traffic -----------------------------------------------------
-    @staticmethod
-    def _to_host(*tensors):
-        return [t.cpu() for t in tensors]
+    def _to_host(self, *tensors):
+        return self._runtime().staging.to_host("enc", *tensors)
 
     def _decode_plane_fn(self, rt):
         def decode_plane(idx_dev):
-            idx = idx_dev.cpu()
-            out = torch.empty(idx.shape, dtype=torch.int16)
+            (idx,) = rt.staging.to_host("dec_idx", idx_dev)
+            out = rt.staging.host_buf("dec_sym", idx.shape, torch.int16)
             rt.coder.decode_planes(idx, rt.tables["y"], out)
-            return out.to(rt.B.device)
+            return out.to(rt.B.device, non_blocking=True)
         return decode_plane
 
     def _decode_z(self, rt, table_name, C, zs):
-        out = torch.empty((1, C, zs[0], zs[1]), dtype=torch.int16)
+        out = rt.staging.host_buf("dec_z", (1, C, zs[0], zs[1]), torch.int16)
         rt.coder.decode_channels(C, zs[0] * zs[1], rt.tables[table_name], out)
-        return rt.B.symbols_to_latent(out.to(rt.B.device), 1, zs[0], zs[1], C)
+        return rt.B.symbols_to_latent(out.to(rt.B.device, non_blocking=True), 1, zs[0], zs[1], C)
 
 
 # ==========================================================================================
@@ -638,12 +675,12 @@ class DMC(CompressionModel):
         """Host side of the decoder requests: the sequential rANS decoder (GIL released inside)."""
         def service(req):
             if req[0] == "plane":
-                idx = req[1].cpu()
-                out = torch.empty(idx.shape, dtype=torch.int16)
+                (idx,) = rt.staging.to_host("dec_idx", req[1])
+                out = rt.staging.host_buf("dec_sym", idx.shape, torch.int16)
                 rt.coder.decode_planes(idx, rt.tables["y"], out)
                 return out
             _, name, C, zs = req
-            out = torch.empty((1, C, zs[0], zs[1]), dtype=torch.int16)
+            out = rt.staging.host_buf("dec_z:" + name, (1, C, zs[0], zs[1]), torch.int16)
             rt.coder.decode_channels(C, zs[0] * zs[1], rt.tables[name], out)
             return out
         return service
