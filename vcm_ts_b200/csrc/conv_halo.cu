@@ -48,6 +48,7 @@ struct HaloGeom {
   int bn, cout_p, tmem_cols, scalar_epi;
   int nacc;   // TMEM accumulator ring depth (2 or 4): lets the MMA warp run ahead of both epilogue warpgroups
   int epi_base, bar_base, bias_base, epi_bw;
+  int tma_epi;   // 64-channel bf16 tiles leave through a TMA store (tc_epilogue.cuh epilogue_warp_tma)
   uint32_t idesc;
 };
 
@@ -229,7 +230,8 @@ __device__ __forceinline__ void mma_role_split(const HaloGeom& G, const HaloBars
 template <int CHUNK>
 __global__ void __launch_bounds__(H_THREADS, 1)
 conv_halo_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
-                 const ConvParams P, const HaloGeom G) {
+                 const __grid_constant__ CUtensorMap tmY, const __grid_constant__ CUtensorMap tmY2,
+                 const __grid_constant__ CUtensorMap tmR, const ConvParams P, const HaloGeom G) {
   constexpr uint32_t LAYOUT = CHUNK == 64 ? 2u : (CHUNK == 32 ? 4u : 6u);
   constexpr uint32_t ROWB = CHUNK * 2u;      // bytes per pixel row of the A tile / per weight row
   constexpr int KSTEPS = CHUNK / 16;
@@ -243,7 +245,8 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   uint64_t* bempty = bfull + H_MAX_B;
   uint64_t* tfull = bempty + H_MAX_B;
   uint64_t* tempty = tfull + H_MAX_ACC;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + H_MAX_ACC);
+  uint64_t* rfull = tempty + H_MAX_ACC;      // [2]: residual tile of epilogue warpgroup g has landed
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(rfull + 2);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int sp_tiles = G.tiles_x * G.tiles_y;
@@ -255,6 +258,13 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     for (int s = 0; s < H_MAX_A; ++s) { mbar_init(&afull[s], 1); mbar_init(&aempty[s], 1); }
     for (int s = 0; s < H_MAX_B; ++s) { mbar_init(&bfull[s], 1); mbar_init(&bempty[s], 1); }
     for (int a = 0; a < H_MAX_ACC; ++a) { mbar_init(&tfull[a], 1); mbar_init(&tempty[a], 4); }
+    mbar_init(&rfull[0], 1);
+    mbar_init(&rfull[1], 1);
+    if (G.tma_epi) {
+      prefetch_tmap(&tmY);
+      if (P.flags & VCM_CONV_OUT2) prefetch_tmap(&tmY2);
+      if (P.flags & (VCM_CONV_RES | VCM_CONV_RES_SCALE)) prefetch_tmap(&tmR);
+    }
     fence_barrier_init();
   }
   if (warp == 1) tmem_alloc(tmem_slot, (uint32_t)G.tmem_cols);
@@ -358,6 +368,49 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     const int q = warp & 3;   // TMEM lane quarter this warp may access
     const uint32_t stage = smem_u32(smem + G.epi_base) + (uint32_t)((warp - 4) * EPI_STAGE_FLOATS * 4);
     pdl_wait();   // residuals / SE scales are read and outputs written only after the predecessor finished
+    if (G.tma_epi) {
+      // this warpgroup's k-th tile: item local = 2 * (k / mh) + g, half h = k % mh
+      EpiTma E;
+      E.tmY = &tmY; E.tmY2 = &tmY2; E.tmR = &tmR;
+      E.obuf = smem_u32(smem + G.epi_base) + (uint32_t)(g * 2 * EPI_TMA_TILE_BYTES);
+      E.rbuf = E.obuf + (uint32_t)EPI_TMA_TILE_BYTES;
+      E.rfull = &rfull[g];
+      E.rphase = 0;
+      E.leader = (q == 0 && lane == 0);
+      const bool has_res = P.flags & (VCM_CONV_RES | VCM_CONV_RES_SCALE);
+      auto tile = [&](int k, int& item, int& h, int& n, int& oy0, int& ox0, int& cb) -> bool {
+        const int loc = 2 * (k / G.mh) + g;
+        h = k % G.mh;
+        item = blockIdx.x + loc * gridDim.x;
+        if (item >= G.num_items) return false;
+        const int nt = item % G.n_tiles, sp = item / G.n_tiles;
+        n = sp / sp_tiles;
+        const int rem = sp - n * sp_tiles;
+        ox0 = (rem % G.tiles_x) * HTW;
+        oy0 = (rem / G.tiles_x) * (HTH * G.mh) + h * HTH;
+        cb = nt * G.bn;
+        return true;
+      };
+      int item, h, n, oy0, ox0, cb;
+      bool ok = tile(0, item, h, n, oy0, ox0, cb);
+      if (ok && has_res && E.leader) epi_tma_prefetch_res(E, cb, ox0, oy0, n);
+      for (int k = 0; ok; ++k) {
+        int item2, h2, n2, oy2, ox2, cb2;
+        const bool ok2 = tile(k + 1, item2, h2, n2, oy2, ox2, cb2);
+        const int loc = 2 * (k / G.mh) + g;
+        const int ab = loc % G.nacc;
+        const uint32_t acc_phase = (uint32_t)(loc / G.nacc) & 1u;
+        const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)((ab * G.mh + h) * G.bn);
+        if (g == 0)
+          epilogue_warp_tma<1>(P, E, n, oy0, ox0, cb, taddr, q, lane, h == 0 ? &tfull[ab] : nullptr, acc_phase,
+                               h == G.mh - 1 ? &tempty[ab] : nullptr, bias_smem, ok2, n2, oy2, ox2, cb2);
+        else
+          epilogue_warp_tma<2>(P, E, n, oy0, ox0, cb, taddr, q, lane, h == 0 ? &tfull[ab] : nullptr, acc_phase,
+                               h == G.mh - 1 ? &tempty[ab] : nullptr, bias_smem, ok2, n2, oy2, ox2, cb2);
+        ok = ok2; item = item2; h = h2; n = n2; oy0 = oy2; ox0 = ox2; cb = cb2;
+      }
+      if (E.leader) tma_store_wait_all();
+    } else {
     int local = 0;
     for (int item = blockIdx.x; item < G.num_items; item += gridDim.x, ++local) {
       if ((local & 1) != g) continue;
@@ -391,6 +444,7 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             epilogue_thread_scalar<bf>(P, G.bn, n, oy, ox, cbase, taddr, wait, acc_phase, release);
         }
       }
+    }
     }
   }
 
@@ -437,8 +491,13 @@ int vcm_conv_halo_launch(const vcm_conv_desc* d, const ConvParams& P, const void
   G.b_slot_bytes = round_up(G.b_bytes, 1024);
   const int slabs = G.ntaps * G.nchunks * (G.split ? 3 : 1);
   const int bias_bytes = round_up((G.cout_p < EPI_BIAS_MAX ? G.cout_p : EPI_BIAS_MAX) * 4, 128);
-  const int budget = SMEM_LIMIT - 1024 - 512 - bias_bytes - EPI_STAGE_BYTES;   // alignment slack, barriers, bias, staging
   G.scalar_epi = tc_epilogue_mode(d, P);
+  static const bool no_tma_epi = getenv("VCM_TC_NO_TMA_EPI") && getenv("VCM_TC_NO_TMA_EPI")[0] == '1';
+  G.tma_epi = (!no_tma_epi && !G.split && G.scalar_epi == 0 && G.bn == 64 && P.Cout % 64 == 0 &&
+               !(P.flags & (VCM_CONV_PIXEL_SHUFFLE | VCM_CONV_RES2)) &&
+               !((P.flags & VCM_CONV_OUT2) && (P.flags & (VCM_CONV_RES | VCM_CONV_RES_SCALE)))) ? 1 : 0;
+  const int epi_bytes = G.tma_epi ? EPI_TMA_BYTES : EPI_STAGE_BYTES;
+  const int budget = SMEM_LIMIT - 1024 - 512 - bias_bytes - epi_bytes;   // alignment slack, barriers, bias, staging
 
   auto a_stage = [&](int mh) { return (G.split ? 3 : 1) * round_up(G.hw * (HTH * mh + P.K - 1) * chunk * 2, 1024); };
   // resident weights if they leave room for >= 3 activation stages
@@ -516,9 +575,31 @@ int vcm_conv_halo_launch(const vcm_conv_desc* d, const ConvParams& P, const void
       return 1;
     }
   }
+  CUtensorMap tmY, tmY2, tmR;
+  memset(&tmY, 0, sizeof(tmY));
+  memset(&tmY2, 0, sizeof(tmY2));
+  memset(&tmR, 0, sizeof(tmR));
+  if (G.tma_epi) {
+    auto out_map = [&](CUtensorMap* tm, const void* base, int cs) -> bool {
+      cuuint64_t dims[4] = {(cuuint64_t)P.Cout, (cuuint64_t)P.Wo, (cuuint64_t)P.Ho, (cuuint64_t)P.N};
+      cuuint64_t strides[3] = {(cuuint64_t)cs * 2, (cuuint64_t)P.Wo * cs * 2, (cuuint64_t)P.Ho * P.Wo * cs * 2};
+      cuuint32_t box[4] = {64, (cuuint32_t)HTW, (cuuint32_t)HTH, 1};
+      cuuint32_t estr[4] = {1, 1, 1, 1};
+      return enc(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(base), dims, strides, box, estr,
+                 CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                 CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+    };
+    bool ok = out_map(&tmY, P.y, P.out_cs);
+    if (ok && (P.flags & VCM_CONV_OUT2)) ok = out_map(&tmY2, P.y2, P.out2_cs);
+    if (ok && (P.flags & (VCM_CONV_RES | VCM_CONV_RES_SCALE))) ok = out_map(&tmR, P.res, P.res_cs);
+    if (!ok) {
+      vcm_set_error("vcm_conv_halo_launch: cuTensorMapEncodeTiled(output) failed");
+      return 1;
+    }
+  }
   const int b_slots = G.resident ? slabs : G.b_stages;
   G.epi_base = G.b_base + b_slots * G.b_slot_bytes;
-  G.bar_base = G.epi_base + EPI_STAGE_BYTES;
+  G.bar_base = G.epi_base + epi_bytes;
   G.bias_base = G.bar_base + 512;
   int smem_bytes = G.bias_base + bias_bytes + 1024;
   if (smem_bytes < 120 * 1024) smem_bytes = 120 * 1024;   // one CTA per SM (TMEM is per CTA)
@@ -541,7 +622,7 @@ int vcm_conv_halo_launch(const vcm_conv_desc* d, const ConvParams& P, const void
     attr[0].val.programmaticStreamSerializationAllowed = 1;                                              \
     cfg.attrs = attr;                                                                                    \
     cfg.numAttrs = (P.flags & VCM_CONV_PDL) ? 1 : 0;                                                     \
-    cudaLaunchKernelEx(&cfg, conv_halo_kernel<CH>, tmA, tmB, P, G);                                      \
+    cudaLaunchKernelEx(&cfg, conv_halo_kernel<CH>, tmA, tmB, tmY, tmY2, tmR, P, G);                      \
   } while (0)
   if (chunk == 64) LAUNCH_HALO(64);
   else if (chunk == 32) LAUNCH_HALO(32);

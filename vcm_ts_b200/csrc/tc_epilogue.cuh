@@ -277,6 +277,123 @@ __device__ __forceinline__ void epilogue_warp_vec(const ConvParams& P, int bn, i
   }
 }
 
+// ------------------------------------------------------------------------------- TMA-store path
+// Measured (scripts/conv_bench.py, round 2): with its global loads / stores switched off the vector path above
+// still costs ~3000 cycles per 128 x 64 tile -- ~1100 warp instructions of TMEM -> registers -> staging ->
+// registers, address arithmetic and per-lane 16-byte global accesses -- which is MORE than the 1980 cycles the 36
+// MMAs of a 3x3 64->64 tile take: every N = 64 layer was epilogue-bound.  Here the tile leaves through ONE
+// TMA store: each thread (= one pixel = one TMEM lane) converts its 64 channels and writes them as eight
+// 16-byte chunks into a 128B-swizzled [128 px][64 ch] bf16 image of the tile in shared memory (conflict
+// free), a warpgroup barrier, one elected thread issues cp.async.bulk.tensor (the tensor map clips the tile at
+// the image edge).  The residual operand arrives the same way, by a TMA load issued one item ahead, and is
+// read back row-wise from shared memory.  Same float operations in the same order as the vector path.
+// Handles: bf16 output, N tile of exactly 64 channels, POST_ACT, RES / RES_SCALE, OUT2; not PixelShuffle, RES2.
+constexpr int EPI_TMA_TILE_BYTES = 128 * 128;                 // [128 px][64 ch] bf16
+constexpr int EPI_TMA_BYTES = 4 * EPI_TMA_TILE_BYTES;         // per warpgroup: output tile + residual tile
+
+struct EpiTma {
+  const CUtensorMap *tmY, *tmY2, *tmR;
+  uint32_t obuf, rbuf;       // shared-window addresses of this warpgroup's output / residual (or twin) tiles
+  uint64_t* rfull;           // residual tile landed
+  uint32_t rphase;
+  bool leader;               // the one thread of the warpgroup that issues TMA operations
+};
+
+__device__ __forceinline__ void epi_tma_prefetch_res(const EpiTma& E, int c, int x0, int y0, int n) {
+  mbar_expect_tx(E.rfull, (uint32_t)EPI_TMA_TILE_BYTES);
+  tma_load_4d(E.rbuf, E.tmR, E.rfull, c, x0, y0, n);
+}
+
+// One warp's 32 pixels of a 128-pixel x 64-channel tile (wq = TMEM lane quarter = tile rows 32*wq ..).
+// next_*: the coordinates of this warpgroup's next tile (residual prefetch), has_next = false at the end.
+// The 64 channels are processed as two halves of 32 to keep the register footprint small.  OUT2 (activated
+// twin) is only taken together with "no residual": the twin tile then uses the idle residual buffer.
+template <int BAR>
+__device__ __forceinline__ void epilogue_warp_tma(const ConvParams& P, EpiTma& E, int n, int oy0, int ox0, int cbase,
+                                                  uint32_t taddr, int wq, int lane, uint64_t* wait, uint32_t parity,
+                                                  uint64_t* release, uint32_t bias_smem, bool has_next, int nn,
+                                                  int noy0, int nox0, int ncbase) {
+  const bool has_res = P.flags & (VCM_CONV_RES | VCM_CONV_RES_SCALE);
+  const bool twin = P.flags & VCM_CONV_OUT2;
+  const float slope = (P.flags & VCM_CONV_POST_ACT) ? P.post_slope : 1.0f;
+  const int m = wq * 32 + lane;                 // tile row = pixel
+  const uint32_t row = (uint32_t)m * 128u;
+  const uint32_t sw = (uint32_t)(m & 7);
+  // the previous tile's stores must have finished reading the staging tiles before they are overwritten
+  if (E.leader) tma_store_wait_read();
+  named_bar_sync(BAR, 128);
+  if (wait) {
+    mbar_wait(wait, parity);
+    tc_fence_after();
+  }
+  if (has_res) {
+    mbar_wait(E.rfull, E.rphase);
+    E.rphase ^= 1u;
+  }
+#pragma unroll
+  for (int half = 0; half < 2; ++half) {
+    float v[32];
+    tmem_load_block<32>(taddr + (uint32_t)(32 * half), v);
+    if (half == 1 && release) {      // last TMEM read of the tile
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(release);
+    }
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const float4 b = lds128(bias_smem + (uint32_t)(cbase + 32 * half + 4 * j) * 4u);
+      v[4 * j] = leaky01(v[4 * j] + b.x, slope);
+      v[4 * j + 1] = leaky01(v[4 * j + 1] + b.y, slope);
+      v[4 * j + 2] = leaky01(v[4 * j + 2] + b.z, slope);
+      v[4 * j + 3] = leaky01(v[4 * j + 3] + b.w, slope);
+    }
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const uint32_t chunk = ((uint32_t)(4 * half + j) ^ sw) << 4;
+      if (has_res) {
+        uint4 rr;
+        asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];"
+                     : "=r"(rr.x), "=r"(rr.y), "=r"(rr.z), "=r"(rr.w)
+                     : "r"(E.rbuf + row + chunk));
+        float r[8];
+        unpack8(rr, r);
+        if (P.flags & VCM_CONV_RES) {
+#pragma unroll
+          for (int i = 0; i < 8; ++i) v[8 * j + i] = r[i] + v[8 * j + i];
+        } else {
+          const float* sp = P.res_scale + (size_t)n * P.Cout + cbase + 32 * half + 8 * j;
+          const float4 s0 = __ldg(reinterpret_cast<const float4*>(sp));
+          const float4 s1 = __ldg(reinterpret_cast<const float4*>(sp + 4));
+          const float sc[8] = {s0.x, s0.y, s0.z, s0.w, s1.x, s1.y, s1.z, s1.w};
+#pragma unroll
+          for (int i = 0; i < 8; ++i) v[8 * j + i] = v[8 * j + i] + __fmul_rn(r[i], sc[i]);
+        }
+      }
+      const uint4 o = pack8(v + 8 * j);
+      asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(E.obuf + row + chunk), "r"(o.x), "r"(o.y),
+                   "r"(o.z), "r"(o.w)
+                   : "memory");
+      if (twin) {
+        float t[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) t[i] = leaky01(v[8 * j + i], P.out2_slope);
+        const uint4 o2 = pack8(t);
+        asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(E.rbuf + row + chunk), "r"(o2.x), "r"(o2.y),
+                     "r"(o2.z), "r"(o2.w)
+                     : "memory");
+      }
+    }
+  }
+  fence_proxy_async();
+  named_bar_sync(BAR, 128);        // tiles complete; everybody is done reading the residual tile
+  if (E.leader) {
+    tma_store_4d(E.tmY, E.obuf, cbase, ox0, oy0, n);
+    if (twin) tma_store_4d(E.tmY2, E.rbuf, cbase, ox0, oy0, n);
+    tma_store_commit();
+    if (has_res && has_next) epi_tma_prefetch_res(E, ncbase, nox0, noy0, nn);
+  }
+}
+
 // ------------------------------------------------------------------------------- scalar path
 // thread = pixel (oy, ox); loops over the bn columns of the slab
 // nsum > 1 (split-bf16 parity mode): the item owns nsum accumulators of bn columns each ([0] = correction
