@@ -336,6 +336,7 @@ def build_workers(n, precision, sd_p, sd_i, dev, graphs, gop):
         dmc.update(force=True)
         intra.update(force=True)
         dmc.set_cuda_graphs(bool(graphs))
+        intra.set_cuda_graphs(bool(graphs))
         workers.append(dict(dmc=dmc, intra=intra, stream=torch.cuda.Stream(dev), bits=0,
                             host_out=torch.empty((gop, H, W, 3), dtype=torch.uint8).pin_memory()))
     return workers

@@ -166,6 +166,18 @@ int vcm_flow_up2(const float* src, float* dst, int32_t N, int32_t H, int32_t W,
                  int32_t src_cstride, int32_t dst_cstride, float gain, void* stream);
 int vcm_flow_down2(const float* src, float* dst, int32_t N, int32_t H, int32_t W,
                    int32_t src_cstride, int32_t dst_cstride, float gain, void* stream);
+/* Fused SpyNet glue (ME_Spynet.forward, video_net.py:118-146), bit-identical to chains of the four entries above.
+ * vcm_spynet_pyramid: NCHW fp32 frames x (im1) and ref (im2), H and W multiples of 8 -> all four pyramid levels
+ *   of both (avg_pool2d three times, :131-133): im1 level k into channels 0..2 of the 8-channel fp32 level-input
+ *   buffer lvl[k] [N, H>>k, W>>k, 8], im2 level k into im2[k] [N, H>>k, W>>k, 3].
+ * vcm_spynet_level_input: one level's network input (:139-146): flow_up = bilinear_x2(flow_prev) * 2 into
+ *   channels 6,7 of lvl, flow_warp(im2 level, flow_up) into channels 3..5 (0..2 hold im1 already); buf16 (may
+ *   be NULL): the same eight channels as bf16 padded to 16 (tensor-core first layer).
+ *   flow_prev: [N, h/2, w/2] 2-channel fp32 view (prev_cstride channels per pixel).                        */
+int vcm_spynet_pyramid(const float* x, const float* ref, float* const* lvl, float* const* im2, int32_t N,
+                       int32_t H, int32_t W, void* stream);
+int vcm_spynet_level_input(const float* flow_prev, const float* im2, float* lvl, void* buf16, int32_t N,
+                           int32_t h, int32_t w, int32_t prev_cstride, void* stream);
 /* feature view (dtype) warped by a 2-channel fp32 flow view: bilinear, border, align_corners */
 int vcm_flow_warp(const void* feat, const float* flow, void* out, int32_t N, int32_t H,
                   int32_t W, int32_t C, int32_t feat_cstride, int32_t flow_cstride,

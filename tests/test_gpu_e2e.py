@@ -502,6 +502,7 @@ def test_cuda_graph_mode_equals_eager_coding(precision):
     want_blobs, want_rec = serial(*_models(precision))
     dmc, intra = _models(precision)
     dmc.set_cuda_graphs(True)
+    intra.set_cuda_graphs(True)       # the I-frame too: encoder graph + decoder chain (3 segments)
     s = torch.cuda.Stream(dev)
     with torch.cuda.stream(s):
         for gop in range(3):
@@ -512,6 +513,7 @@ def test_cuda_graph_mode_equals_eager_coding(precision):
                 assert torch.equal(recs[t], want_rec[t]), (gop, t)
     B = dmc._rt.B
     assert B.graph_replays > 0 and len(dmc._rt.programs.progs) == 4   # enc/dec x first/steady P-frame
+    assert intra._rt.B.graph_replays > 0 and len(intra._rt.programs.progs) == 2
     # also from the legacy default stream (capture runs on a side stream)
     blobs, recs = serial(dmc, intra)
     assert blobs == want_blobs and all(torch.equal(a, b) for a, b in zip(recs, want_rec))
@@ -519,6 +521,7 @@ def test_cuda_graph_mode_equals_eager_coding(precision):
     enc, dec = _models(precision), _models(precision)
     enc[0].set_cuda_graphs(True)
     dec[0].set_cuda_graphs(True)
+    dec[1].set_cuda_graphs(True)
     pipe = GopPipeline(enc, dec, dev)
     got = {}
     for gop in range(3):

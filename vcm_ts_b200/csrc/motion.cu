@@ -233,7 +233,178 @@ __global__ void __launch_bounds__(256) flow_warp8_bf16_kernel(const __nv_bfloat1
   }
 }
 
+// ------------------------------------------------------------------------------------------------
+// Fused SpyNet glue (video_net.py:118-146).  Same arithmetic, statement by statement, as the separate
+// kernels above, so the results are bit-identical to avgpool2 / flow_up2 / flow_warp chains.
+//
+// spynet_pyramid: both NCHW fp32 frames -> the three coarser levels of both image pyramids plus the NHWC
+// level-0 copies, in ONE pass: a thread owns one 8x8 block of one colour plane of one image, i.e. one pixel
+// of the coarsest level (avg_pool2d applied three times, each level from the rounded level below).
+//   im1 level k -> lvl[k] channel c (8-channel level-input buffers), im2 level k -> im2[k] (3 channels)
+struct PyrOut {
+  float* lvl[4];
+  float* im2[4];
+};
+
+__global__ void spynet_pyramid_kernel(const float* __restrict__ x, const float* __restrict__ ref, PyrOut O, int N,
+                                      int H, int W) {
+  const int H3 = H / 8, W3 = W / 8;
+  const int64_t total = (int64_t)N * 2 * 3 * H3 * W3;
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total;
+       i += (int64_t)gridDim.x * blockDim.x) {
+    const int bx = (int)(i % W3);
+    int64_t r = i / W3;
+    const int by = (int)(r % H3);
+    r /= H3;
+    const int c = (int)(r % 3);
+    r /= 3;
+    const int img = (int)(r % 2);
+    const int n = (int)(r / 2);
+    const float* src = (img == 0 ? x : ref) + ((int64_t)n * 3 + c) * H * W + (int64_t)(8 * by) * W + 8 * bx;
+    float l0[8][8];
+#pragma unroll
+    for (int yy = 0; yy < 8; ++yy) {
+      const float4 a = __ldg(reinterpret_cast<const float4*>(src + (int64_t)yy * W));
+      const float4 b = __ldg(reinterpret_cast<const float4*>(src + (int64_t)yy * W + 4));
+      l0[yy][0] = a.x; l0[yy][1] = a.y; l0[yy][2] = a.z; l0[yy][3] = a.w;
+      l0[yy][4] = b.x; l0[yy][5] = b.y; l0[yy][6] = b.z; l0[yy][7] = b.w;
+    }
+    float* d0 = img == 0 ? O.lvl[0] : O.im2[0];
+    const int cs = img == 0 ? 8 : 3;
+#pragma unroll
+    for (int yy = 0; yy < 8; ++yy)
+#pragma unroll
+      for (int xx = 0; xx < 8; ++xx)
+        d0[(((int64_t)n * H + 8 * by + yy) * W + 8 * bx + xx) * cs + c] = l0[yy][xx];
+    float l1[4][4], l2[2][2];
+#pragma unroll
+    for (int yy = 0; yy < 4; ++yy)
+#pragma unroll
+      for (int xx = 0; xx < 4; ++xx) {
+        float v = l0[2 * yy][2 * xx];
+        v = __fadd_rn(v, l0[2 * yy][2 * xx + 1]);
+        v = __fadd_rn(v, l0[2 * yy + 1][2 * xx]);
+        v = __fadd_rn(v, l0[2 * yy + 1][2 * xx + 1]);
+        l1[yy][xx] = __fdiv_rn(v, 4.f);
+      }
+    float* d1 = img == 0 ? O.lvl[1] : O.im2[1];
+#pragma unroll
+    for (int yy = 0; yy < 4; ++yy)
+#pragma unroll
+      for (int xx = 0; xx < 4; ++xx)
+        d1[(((int64_t)n * (H / 2) + 4 * by + yy) * (W / 2) + 4 * bx + xx) * cs + c] = l1[yy][xx];
+#pragma unroll
+    for (int yy = 0; yy < 2; ++yy)
+#pragma unroll
+      for (int xx = 0; xx < 2; ++xx) {
+        float v = l1[2 * yy][2 * xx];
+        v = __fadd_rn(v, l1[2 * yy][2 * xx + 1]);
+        v = __fadd_rn(v, l1[2 * yy + 1][2 * xx]);
+        v = __fadd_rn(v, l1[2 * yy + 1][2 * xx + 1]);
+        l2[yy][xx] = __fdiv_rn(v, 4.f);
+      }
+    float* d2 = img == 0 ? O.lvl[2] : O.im2[2];
+#pragma unroll
+    for (int yy = 0; yy < 2; ++yy)
+#pragma unroll
+      for (int xx = 0; xx < 2; ++xx)
+        d2[(((int64_t)n * (H / 4) + 2 * by + yy) * (W / 4) + 2 * bx + xx) * cs + c] = l2[yy][xx];
+    float v = l2[0][0];
+    v = __fadd_rn(v, l2[0][1]);
+    v = __fadd_rn(v, l2[1][0]);
+    v = __fadd_rn(v, l2[1][1]);
+    float* d3 = img == 0 ? O.lvl[3] : O.im2[3];
+    d3[(((int64_t)n * H3 + by) * W3 + bx) * cs + c] = __fdiv_rn(v, 4.f);
+  }
+}
+
+// spynet_level_input: one level's network input in one pass (video_net.py:139-146):
+//   flow_up = bilinear_x2(flow_prev) * 2 -> channels 6,7 ; warp(im2_level, flow_up) -> channels 3..5
+// of the 8-channel fp32 level buffer whose channels 0..2 already hold im1_level, and (buf16 != null) the
+// bf16 copy of all eight channels padded to 16 that the tcgen05 7x7 conv reads.  One thread per pixel.
+__global__ void spynet_level_input_kernel(const float* __restrict__ flow_prev, const float* __restrict__ im2,
+                                          float* __restrict__ lvl, __nv_bfloat16* __restrict__ buf16, int N, int h,
+                                          int w, int prev_cs) {
+  const int hp = h / 2, wp = w / 2;
+  const int64_t total = (int64_t)N * h * w;
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total;
+       i += (int64_t)gridDim.x * blockDim.x) {
+    const int ox = (int)(i % w);
+    int64_t p = i / w;
+    const int oy = (int)(p % h);
+    const int n = (int)(p / h);
+    // ---- flow_up2 (gain 2)
+    float sy = fmaxf((oy + 0.5f) * 0.5f - 0.5f, 0.f);
+    float sx = fmaxf((ox + 0.5f) * 0.5f - 0.5f, 0.f);
+    const int y0 = (int)sy, x0 = (int)sx;
+    const int y1 = y0 + (y0 < hp - 1 ? 1 : 0), x1 = x0 + (x0 < wp - 1 ? 1 : 0);
+    const float ly = sy - y0, lx = sx - x0;
+    const float hy = 1.f - ly, hx = 1.f - lx;
+    const float* b = flow_prev + (int64_t)n * hp * wp * prev_cs;
+    float uv[2];
+#pragma unroll
+    for (int c = 0; c < 2; ++c) {
+      const float p00 = __ldg(b + ((int64_t)y0 * wp + x0) * prev_cs + c);
+      const float p01 = __ldg(b + ((int64_t)y0 * wp + x1) * prev_cs + c);
+      const float p10 = __ldg(b + ((int64_t)y1 * wp + x0) * prev_cs + c);
+      const float p11 = __ldg(b + ((int64_t)y1 * wp + x1) * prev_cs + c);
+      const float top = __fadd_rn(__fmul_rn(hx, p00), __fmul_rn(lx, p01));
+      const float bot = __fadd_rn(__fmul_rn(hx, p10), __fmul_rn(lx, p11));
+      uv[c] = __fmul_rn(__fadd_rn(__fmul_rn(hy, top), __fmul_rn(ly, bot)), 2.f);
+    }
+    // ---- warp of the 3-channel reference level
+    const WarpTaps t = warp_taps(uv[0], uv[1], ox, oy, w, h);
+    const float* f = im2 + (int64_t)n * h * w * 3;
+    float o[8];
+    float* L = lvl + i * 8;
+    o[0] = L[0]; o[1] = L[1]; o[2] = L[2];
+#pragma unroll
+    for (int c = 0; c < 3; ++c)
+      o[3 + c] = warp_mix(t, __ldg(f + ((int64_t)t.y0 * w + t.x0) * 3 + c), __ldg(f + ((int64_t)t.y0 * w + t.x1) * 3 + c),
+                          __ldg(f + ((int64_t)t.y1 * w + t.x0) * 3 + c), __ldg(f + ((int64_t)t.y1 * w + t.x1) * 3 + c));
+    o[6] = uv[0];
+    o[7] = uv[1];
+    *reinterpret_cast<float4*>(L + 4) = make_float4(o[4], o[5], o[6], o[7]);
+    L[3] = o[3];
+    if (buf16) {
+      __nv_bfloat162 h2[4];
+#pragma unroll
+      for (int k = 0; k < 4; ++k) h2[k] = __floats2bfloat162_rn(o[2 * k], o[2 * k + 1]);
+      uint4* d = reinterpret_cast<uint4*>(buf16 + i * 16);
+      d[0] = *reinterpret_cast<uint4*>(h2);
+      d[1] = make_uint4(0u, 0u, 0u, 0u);
+    }
+  }
+}
+
 }  // namespace
+
+extern "C" int vcm_spynet_pyramid(const float* x, const float* ref, float* const* lvl, float* const* im2, int32_t N,
+                                  int32_t H, int32_t W, void* stream) {
+  VCM_CHECK_ARG(x && ref && lvl && im2 && N > 0 && H % 8 == 0 && W % 8 == 0, "bad argument (H, W multiples of 8)");
+  VCM_CHECK_ARG(((uintptr_t)x & 15) == 0 && ((uintptr_t)ref & 15) == 0, "frames must be 16-byte aligned");
+  PyrOut O;
+  for (int k = 0; k < 4; ++k) {
+    VCM_CHECK_ARG(lvl[k] && im2[k], "null level buffer");
+    O.lvl[k] = lvl[k];
+    O.im2[k] = im2[k];
+  }
+  const int64_t total = (int64_t)N * 6 * (H / 8) * (W / 8);
+  spynet_pyramid_kernel<<<ew_grid(total), 128, 0, (cudaStream_t)stream>>>(x, ref, O, N, H, W);
+  VCM_CHECK_LAUNCH();
+  return 0;
+}
+
+extern "C" int vcm_spynet_level_input(const float* flow_prev, const float* im2, float* lvl, void* buf16, int32_t N,
+                                      int32_t h, int32_t w, int32_t prev_cstride, void* stream) {
+  VCM_CHECK_ARG(flow_prev && im2 && lvl && N > 0 && h > 1 && w > 1 && h % 2 == 0 && w % 2 == 0, "bad argument");
+  VCM_CHECK_ARG(((uintptr_t)lvl & 15) == 0 && ((uintptr_t)buf16 & 15) == 0, "level buffers must be 16-byte aligned");
+  const int64_t total = (int64_t)N * h * w;
+  spynet_level_input_kernel<<<ew_grid(total), 256, 0, (cudaStream_t)stream>>>(
+      flow_prev, im2, lvl, (__nv_bfloat16*)buf16, N, h, w, prev_cstride);
+  VCM_CHECK_LAUNCH();
+  return 0;
+}
 
 extern "C" int vcm_avgpool2(const float* src, float* dst, int32_t N, int32_t H, int32_t W, int32_t C,
                             int32_t src_cstride, int32_t dst_cstride, void* stream) {

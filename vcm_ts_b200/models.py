@@ -855,14 +855,54 @@ class IntraNoAR(CompressionModel):
             return {"x_hat": x_hat, "mse": mse, "bit": bits.item(), "bpp": bpp_y + bpp_z,
                     "bpp_y": bpp_y, "bpp_z": bpp_z}
 
+    # ---- captured programs (set_cuda_graphs): static input frame / output reconstruction per resolution
+    def _intra_statics(self, rt, H, W):
+        st = rt.statics.get((H, W, "intra"))
+        if st is None:
+            dev = rt.B.device
+            st = {"x": torch.empty((1, 3, H, W), dtype=F32, device=dev),
+                  "x_hat": torch.empty((1, 3, H, W), dtype=F32, device=dev),
+                  "z_sym": rt.B.empty((1, self.N, H // 64, W // 64), torch.int16)}
+            rt.statics[(H, W, "intra")] = st
+        return st
+
+    def _enc_body(self, rt, x, q_scale):
+        q = self._curr_q(rt, self.q_basic, q_scale, 1)
+        z_sym, _, dp = self._trunk(rt, x, q, False)
+        return (z_sym, *dp["sym"], *dp["idx"])
+        yield   # noqa: unreachable -- makes this a generator (graphs.py)
+
+    def _dec_body(self, rt, z_sym, zs, q_scale, out):
+        g, B = rt.graph, rt.B
+        q = self._curr_q(rt, self.q_basic, q_scale, 1)
+        z_hat = B.symbols_to_latent(z_sym, 1, zs[0], zs[1], self.N)
+        fusion = g.three_convs("y_prior_fusion", g.hyper_synthesis("hyper_dec", z_hat))
+        gen = g.dual_prior_decode_gen(self._scale_table, fusion, self.N, "y_spatial_prior", q)
+        try:
+            idx = next(gen)
+            while True:
+                sym = yield ("plane", idx)
+                idx = gen.send(sym)
+        except StopIteration as e:
+            y_hat = e.value
+        return B.to_nchw(self._synth(rt, y_hat), clamp=(0.0, 1.0), out=out)
+
     @torch.no_grad()
     def compress(self, x, q_scale):
         """image_model.py:148-177.  Stream order: z, y pass 0, y pass 1."""
         rt = self._need_coder()
         assert x.shape[0] == 1, "the bitstream path is batch 1 (entropy_models.py:186)"
-        q = self._curr_q(rt, self.q_basic, q_scale, 1)
-        z_sym, _, dp = self._trunk(rt, x, q, False)
-        z, s0, s1, i0, i1 = self._to_host(z_sym, *dp["sym"], *dp["idx"])
+        if self._graphs:
+            H, W = x.shape[2:]
+            st = self._intra_statics(rt, H, W)
+            st["x"].copy_(x.detach().to(rt.B.device, F32))
+            syms = rt.programs.run(("ienc", H, W, float(q_scale)),
+                                   lambda: self._enc_body(rt, st["x"], float(q_scale)), None)
+            z, s0, s1, i0, i1 = self._to_host(*syms)
+        else:
+            q = self._curr_q(rt, self.q_basic, q_scale, 1)
+            z_sym, _, dp = self._trunk(rt, x, q, False)
+            z, s0, s1, i0, i1 = self._to_host(z_sym, *dp["sym"], *dp["idx"])
         c = rt.coder
         c.reset_encoder()
         c.encode_channels(z, rt.tables["bit_estimator_z"])
@@ -873,12 +913,28 @@ class IntraNoAR(CompressionModel):
 
     @torch.no_grad()
     def decompress(self, bit_stream, height, width, q_scale):
-        """image_model.py:179-200."""
+        """image_model.py:179-200.  With set_cuda_graphs(True) the returned x_hat is a static buffer of the
+        model that the next decompress() of the same resolution overwrites (use or copy it first)."""
         rt = self._need_coder()
         g, B = rt.graph, rt.B
-        q = self._curr_q(rt, self.q_basic, q_scale, 1)
         rt.coder.set_stream(bit_stream)
         zs = get_downsampled_shape(height, width, 64)
+        if self._graphs:
+            H, W = zs[0] * 64, zs[1] * 64
+            st = self._intra_statics(rt, H, W)
+            z = rt.staging.host_buf("dec_z", (1, self.N, zs[0], zs[1]), torch.int16)
+            rt.coder.decode_channels(self.N, zs[0] * zs[1], rt.tables["bit_estimator_z"], z)
+            st["z_sym"].copy_(z, non_blocking=True)
+
+            def service(req):
+                (idx,) = rt.staging.to_host("dec_idx", req[1])
+                out = rt.staging.host_buf("dec_sym", idx.shape, torch.int16)
+                rt.coder.decode_planes(idx, rt.tables["y"], out)
+                return out
+            rt.programs.run(("idec", H, W, float(q_scale)),
+                            lambda: self._dec_body(rt, st["z_sym"], zs, float(q_scale), st["x_hat"]), service)
+            return {"x_hat": st["x_hat"]}
+        q = self._curr_q(rt, self.q_basic, q_scale, 1)
         z_hat = self._decode_z(rt, "bit_estimator_z", self.N, zs)
         fusion = g.three_convs("y_prior_fusion", g.hyper_synthesis("hyper_dec", z_hat))
         y_hat = g.dual_prior_decode(self._scale_table, fusion, self.N, "y_spatial_prior", q,

@@ -153,6 +153,8 @@ class Graph:
         B = self.B
         N, _, H, W = x_nchw.shape
         L = 4
+        if hasattr(B, "spynet_pyramid") and H % 8 == 0 and W % 8 == 0:
+            return self._spynet_fused(pre, x_nchw, ref_nchw)
         # level buffers hold cat[im1_l, warp(im2_l, flow_up), flow_up] (8 ch, fp32)
         bufs = [B.new(N, H >> k, W >> k, 8, dtype=F32) for k in range(L)]
         im2 = [B.from_nchw(ref_nchw, dtype=F32)]
@@ -179,6 +181,34 @@ class Graph:
             t = self.conv(b + ".conv3", t, post=0.0)
             t = self.conv(b + ".conv4", t, post=0.0)
             flow = self.conv(b + ".conv5", t, res=flow_up, out_dtype=F32)
+        return flow
+
+    def _spynet_fused(self, pre, x_nchw, ref_nchw):
+        """ME_Spynet with the fused glue kernels: ONE pyramid launch for both images and all levels, ONE launch
+        per level for flow_up*2 + warp + concat (+ the bf16 16-channel copy the tensor-core conv1 reads):
+        5 glue launches instead of 20, bit-identical values."""
+        B = self.B
+        N, _, H, W = x_nchw.shape
+        L = 4
+        bufs = [B.new(N, H >> k, W >> k, 8, dtype=F32) for k in range(L)]
+        im2 = [B.new(N, H >> k, W >> k, 3, dtype=F32) for k in range(L)]
+        B.spynet_pyramid(x_nchw, ref_nchw, bufs, im2)
+        flow = B.new(N, (H >> (L - 1)) // 2, (W >> (L - 1)) // 2, 2, dtype=F32, zero=True)
+        for lv in range(L):
+            k = L - 1 - lv
+            buf = bufs[k]
+            b = f"{pre}.moduleBasic.{lv}"
+            if B.use_twin:
+                buf16 = B.new(N, buf.H, buf.W, 16, dtype=B.act_dtype)
+                B.spynet_level_input(flow, im2[k], buf, buf16)
+                t = self.conv(b + ".conv1", buf16, in_map=list(range(8)) + [-1] * 8, post=0.0)
+            else:
+                B.spynet_level_input(flow, im2[k], buf)
+                t = self.conv(b + ".conv1", buf, post=0.0, out_dtype=B.act_dtype)
+            t = self.conv(b + ".conv2", t, post=0.0)
+            t = self.conv(b + ".conv3", t, post=0.0)
+            t = self.conv(b + ".conv4", t, post=0.0)
+            flow = self.conv(b + ".conv5", t, res=buf.sl(6, 8), out_dtype=F32)
         return flow
 
     # ---- common_model.py:104-180 (forward_dual_prior / compress_dual_prior), both passes
