@@ -266,6 +266,14 @@ TC_CASES = [
     (3, 1, 192, 192, 35, 41, 2, 0.2, False, True, False, True, None),     # streamed weights, M = 256 items
     (7, 1, 64, 32, 37, 21, 1, 0.0, False, False, False, False, None),     # ragged 7x7
     (3, 1, 32, 48, 18, 26, 1, None, False, True, False, False, 0.0),      # BN = 48 (BW 16)
+    # TMA-store epilogue (64- / 32-channel tiles): residual by TMA, SE-scaled residual, twin, ragged tile tails
+    (3, 1, 64, 32, 37, 53, 2, 0.01, False, True, False, False, None),
+    (1, 1, 64, 32, 21, 45, 1, None, False, True, True, False, None),
+    (3, 1, 32, 32, 40, 56, 1, 0.01, False, False, False, False, 0.1),
+    (3, 1, 64, 64, 37, 53, 2, 0.01, False, True, True, False, None),
+    (3, 1, 64, 64, 35, 29, 1, None, False, False, False, False, 0.01),
+    (3, 1, 128, 64, 70, 90, 1, 0.1, False, True, False, False, None),     # streamed weights, 256-pixel items
+    (1, 1, 64, 128, 33, 47, 1, None, False, True, False, False, None),    # Cout 128 as two 64-channel N tiles on a small image
 ]
 
 

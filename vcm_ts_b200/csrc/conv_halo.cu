@@ -393,7 +393,10 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       };
       int item, h, n, oy0, ox0, cb;
       bool ok = tile(0, item, h, n, oy0, ox0, cb);
-      if (ok && has_res && E.leader) epi_tma_prefetch_res(E, cb, ox0, oy0, n);
+      if (ok && has_res && E.leader) {
+        if (G.bn == 64) epi_tma_prefetch_res<64>(E, cb, ox0, oy0, n);
+        else epi_tma_prefetch_res<32>(E, cb, ox0, oy0, n);
+      }
       for (int k = 0; ok; ++k) {
         int item2, h2, n2, oy2, ox2, cb2;
         const bool ok2 = tile(k + 1, item2, h2, n2, oy2, ox2, cb2);
@@ -401,12 +404,15 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         const int ab = loc % G.nacc;
         const uint32_t acc_phase = (uint32_t)(loc / G.nacc) & 1u;
         const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)((ab * G.mh + h) * G.bn);
-        if (g == 0)
-          epilogue_warp_tma<1>(P, E, n, oy0, ox0, cb, taddr, q, lane, h == 0 ? &tfull[ab] : nullptr, acc_phase,
-                               h == G.mh - 1 ? &tempty[ab] : nullptr, bias_smem, ok2, n2, oy2, ox2, cb2);
-        else
-          epilogue_warp_tma<2>(P, E, n, oy0, ox0, cb, taddr, q, lane, h == 0 ? &tfull[ab] : nullptr, acc_phase,
-                               h == G.mh - 1 ? &tempty[ab] : nullptr, bias_smem, ok2, n2, oy2, ox2, cb2);
+#define EPI_TMA(BAR, BN)                                                                                        \
+  epilogue_warp_tma<BAR, BN>(P, E, n, oy0, ox0, cb, taddr, q, lane, h == 0 ? &tfull[ab] : nullptr, acc_phase,     \
+                             h == G.mh - 1 ? &tempty[ab] : nullptr, bias_smem, ok2, n2, oy2, ox2, cb2)
+        if (G.bn == 64) {
+          if (g == 0) EPI_TMA(1, 64); else EPI_TMA(2, 64);
+        } else {
+          if (g == 0) EPI_TMA(1, 32); else EPI_TMA(2, 32);
+        }
+#undef EPI_TMA
         ok = ok2; item = item2; h = h2; n = n2; oy0 = oy2; ox0 = ox2; cb = cb2;
       }
       if (E.leader) tma_store_wait_all();
@@ -493,7 +499,7 @@ int vcm_conv_halo_launch(const vcm_conv_desc* d, const ConvParams& P, const void
   const int bias_bytes = round_up((G.cout_p < EPI_BIAS_MAX ? G.cout_p : EPI_BIAS_MAX) * 4, 128);
   G.scalar_epi = tc_epilogue_mode(d, P);
   static const bool no_tma_epi = getenv("VCM_TC_NO_TMA_EPI") && getenv("VCM_TC_NO_TMA_EPI")[0] == '1';
-  G.tma_epi = (!no_tma_epi && !G.split && G.scalar_epi == 0 && G.bn == 64 && P.Cout % 64 == 0 &&
+  G.tma_epi = (!no_tma_epi && !G.split && G.scalar_epi == 0 && (G.bn == 64 || G.bn == 32) && P.Cout % G.bn == 0 &&
                !(P.flags & (VCM_CONV_PIXEL_SHUFFLE | VCM_CONV_RES2)) &&
                !((P.flags & VCM_CONV_OUT2) && (P.flags & (VCM_CONV_RES | VCM_CONV_RES_SCALE)))) ? 1 : 0;
   const int epi_bytes = G.tma_epi ? EPI_TMA_BYTES : EPI_STAGE_BYTES;
@@ -583,11 +589,11 @@ int vcm_conv_halo_launch(const vcm_conv_desc* d, const ConvParams& P, const void
     auto out_map = [&](CUtensorMap* tm, const void* base, int cs) -> bool {
       cuuint64_t dims[4] = {(cuuint64_t)P.Cout, (cuuint64_t)P.Wo, (cuuint64_t)P.Ho, (cuuint64_t)P.N};
       cuuint64_t strides[3] = {(cuuint64_t)cs * 2, (cuuint64_t)P.Wo * cs * 2, (cuuint64_t)P.Ho * P.Wo * cs * 2};
-      cuuint32_t box[4] = {64, (cuuint32_t)HTW, (cuuint32_t)HTH, 1};
+      cuuint32_t box[4] = {(cuuint32_t)G.bn, (cuuint32_t)HTW, (cuuint32_t)HTH, 1};
       cuuint32_t estr[4] = {1, 1, 1, 1};
       return enc(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(base), dims, strides, box, estr,
-                 CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
-                 CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+                 CU_TENSOR_MAP_INTERLEAVE_NONE, G.bn == 64 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B,
+                 CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
     };
     bool ok = out_map(&tmY, P.y, P.out_cs);
     if (ok && (P.flags & VCM_CONV_OUT2)) ok = out_map(&tmY2, P.y2, P.out2_cs);

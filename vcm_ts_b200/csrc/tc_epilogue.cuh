@@ -299,8 +299,9 @@ struct EpiTma {
   bool leader;               // the one thread of the warpgroup that issues TMA operations
 };
 
+template <int BN>
 __device__ __forceinline__ void epi_tma_prefetch_res(const EpiTma& E, int c, int x0, int y0, int n) {
-  mbar_expect_tx(E.rfull, (uint32_t)EPI_TMA_TILE_BYTES);
+  mbar_expect_tx(E.rfull, (uint32_t)(128 * BN * 2));
   tma_load_4d(E.rbuf, E.tmR, E.rfull, c, x0, y0, n);
 }
 
@@ -308,7 +309,8 @@ __device__ __forceinline__ void epi_tma_prefetch_res(const EpiTma& E, int c, int
 // next_*: the coordinates of this warpgroup's next tile (residual prefetch), has_next = false at the end.
 // The 64 channels are processed as two halves of 32 to keep the register footprint small.  OUT2 (activated
 // twin) is only taken together with "no residual": the twin tile then uses the idle residual buffer.
-template <int BAR>
+// BN = 64 (128-byte rows, 128B swizzle) or 32 (64-byte rows, 64B swizzle: chunk ^= (row >> 1) & 3).
+template <int BAR, int BN>
 __device__ __forceinline__ void epilogue_warp_tma(const ConvParams& P, EpiTma& E, int n, int oy0, int ox0, int cbase,
                                                   uint32_t taddr, int wq, int lane, uint64_t* wait, uint32_t parity,
                                                   uint64_t* release, uint32_t bias_smem, bool has_next, int nn,
@@ -317,8 +319,8 @@ __device__ __forceinline__ void epilogue_warp_tma(const ConvParams& P, EpiTma& E
   const bool twin = P.flags & VCM_CONV_OUT2;
   const float slope = (P.flags & VCM_CONV_POST_ACT) ? P.post_slope : 1.0f;
   const int m = wq * 32 + lane;                 // tile row = pixel
-  const uint32_t row = (uint32_t)m * 128u;
-  const uint32_t sw = (uint32_t)(m & 7);
+  const uint32_t row = (uint32_t)m * (uint32_t)(BN * 2);
+  const uint32_t sw = BN == 64 ? (uint32_t)(m & 7) : (uint32_t)((m >> 1) & 3);
   // the previous tile's stores must have finished reading the staging tiles before they are overwritten
   if (E.leader) tma_store_wait_read();
   named_bar_sync(BAR, 128);
@@ -331,10 +333,10 @@ __device__ __forceinline__ void epilogue_warp_tma(const ConvParams& P, EpiTma& E
     E.rphase ^= 1u;
   }
 #pragma unroll
-  for (int half = 0; half < 2; ++half) {
+  for (int half = 0; half < BN / 32; ++half) {
     float v[32];
     tmem_load_block<32>(taddr + (uint32_t)(32 * half), v);
-    if (half == 1 && release) {      // last TMEM read of the tile
+    if (half == BN / 32 - 1 && release) {      // last TMEM read of the tile
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(release);
@@ -390,7 +392,7 @@ __device__ __forceinline__ void epilogue_warp_tma(const ConvParams& P, EpiTma& E
     tma_store_4d(E.tmY, E.obuf, cbase, ox0, oy0, n);
     if (twin) tma_store_4d(E.tmY2, E.rbuf, cbase, ox0, oy0, n);
     tma_store_commit();
-    if (has_res && has_next) epi_tma_prefetch_res(E, ncbase, nox0, noy0, nn);
+    if (has_res && has_next) epi_tma_prefetch_res<BN>(E, ncbase, nox0, noy0, nn);
   }
 }
 
