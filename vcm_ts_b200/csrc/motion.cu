@@ -191,9 +191,10 @@ __global__ void __launch_bounds__(256) flow_warp8_bf16_kernel(const __nv_bfloat1
   const int th = 256 / G / 8;
   constexpr int PP = 2;   // pixels per thread (rows oy and oy + th): both flow loads, then all eight tap loads
   const int g = threadIdx.x % G, pix = threadIdx.x / G;
-  const int ox = blockIdx.x * 8 + (pix & 7);
+  const int ox_raw = blockIdx.x * 8 + (pix & 7);
   const int n = blockIdx.z;
-  if (ox >= W) return;
+  const bool x_in = ox_raw < W;                  // no early exit: the tap shuffles below need whole warps
+  const int ox = x_in ? ox_raw : W - 1;
   const __nv_bfloat16* b = feat + (int64_t)n * H * W * feat_cs + g * 8;
   int oy[PP];
   int64_t p[PP];
@@ -208,7 +209,24 @@ __global__ void __launch_bounds__(256) flow_warp8_bf16_kernel(const __nv_bfloat1
   uint4 v[PP][4];
 #pragma unroll
   for (int j = 0; j < PP; ++j) {
-    t[j] = warp_taps(uv[j].x, uv[j].y, ox, min(oy[j], H - 1), W, H);
+    // the G lanes of a pixel are adjacent: one of them does the coordinate arithmetic (four correctly rounded
+    // divisions among ~70 instructions), the others receive the taps by shuffle
+    if (G > 1 && (G & (G - 1)) == 0) {
+      if (g == 0) t[j] = warp_taps(uv[j].x, uv[j].y, ox, min(oy[j], H - 1), W, H);
+      const int src = (threadIdx.x & 31) & ~(G - 1);
+      t[j].x0 = __shfl_sync(0xffffffffu, t[j].x0, src);
+      t[j].y0 = __shfl_sync(0xffffffffu, t[j].y0, src);
+      t[j].nw = __shfl_sync(0xffffffffu, t[j].nw, src);
+      t[j].ne = __shfl_sync(0xffffffffu, t[j].ne, src);
+      t[j].sw = __shfl_sync(0xffffffffu, t[j].sw, src);
+      t[j].se = __shfl_sync(0xffffffffu, t[j].se, src);
+      t[j].x1_ok = t[j].x0 + 1 <= W - 1;
+      t[j].y1_ok = t[j].y0 + 1 <= H - 1;
+      t[j].x1 = t[j].x1_ok ? t[j].x0 + 1 : W - 1;
+      t[j].y1 = t[j].y1_ok ? t[j].y0 + 1 : H - 1;
+    } else {
+      t[j] = warp_taps(uv[j].x, uv[j].y, ox, min(oy[j], H - 1), W, H);
+    }
     v[j][0] = __ldg(reinterpret_cast<const uint4*>(b + ((int64_t)t[j].y0 * W + t[j].x0) * feat_cs));
     v[j][1] = __ldg(reinterpret_cast<const uint4*>(b + ((int64_t)t[j].y0 * W + t[j].x1) * feat_cs));
     v[j][2] = __ldg(reinterpret_cast<const uint4*>(b + ((int64_t)t[j].y1 * W + t[j].x0) * feat_cs));
@@ -216,7 +234,12 @@ __global__ void __launch_bounds__(256) flow_warp8_bf16_kernel(const __nv_bfloat1
   }
 #pragma unroll
   for (int j = 0; j < PP; ++j) {
-    if (oy[j] >= H) continue;
+    if (oy[j] >= H || !x_in) continue;
+    // ncu (r02): this kernel was instruction-issue bound (issue slots 81 % busy, DRAM 31 %).  The result is
+    // rounded to bf16 anyway, so the four taps are combined with one multiply + three FMAs per channel (masked
+    // taps get weight 0) instead of the seven separately rounded operations of the fp32 kernel.
+    const float wnw = t[j].nw, wne = t[j].x1_ok ? t[j].ne : 0.f, wsw = t[j].y1_ok ? t[j].sw : 0.f,
+                wse = (t[j].x1_ok && t[j].y1_ok) ? t[j].se : 0.f;
     const __nv_bfloat162* h00 = reinterpret_cast<const __nv_bfloat162*>(&v[j][0]);
     const __nv_bfloat162* h01 = reinterpret_cast<const __nv_bfloat162*>(&v[j][1]);
     const __nv_bfloat162* h10 = reinterpret_cast<const __nv_bfloat162*>(&v[j][2]);
@@ -227,7 +250,8 @@ __global__ void __launch_bounds__(256) flow_warp8_bf16_kernel(const __nv_bfloat1
     for (int k = 0; k < 4; ++k) {
       const float2 a = __bfloat1622float2(h00[k]), bb = __bfloat1622float2(h01[k]);
       const float2 cc = __bfloat1622float2(h10[k]), dd = __bfloat1622float2(h11[k]);
-      hr[k] = __floats2bfloat162_rn(warp_mix(t[j], a.x, bb.x, cc.x, dd.x), warp_mix(t[j], a.y, bb.y, cc.y, dd.y));
+      hr[k] = __floats2bfloat162_rn(fmaf(dd.x, wse, fmaf(cc.x, wsw, fmaf(bb.x, wne, a.x * wnw))),
+                                    fmaf(dd.y, wse, fmaf(cc.y, wsw, fmaf(bb.y, wne, a.y * wnw))));
     }
     *reinterpret_cast<uint4*>(out + p[j] * out_cs + g * 8) = r;
   }
