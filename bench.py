@@ -336,7 +336,9 @@ def build_workers(n, precision, sd_p, sd_i, dev, graphs, gop):
         dmc.update(force=True)
         intra.update(force=True)
         dmc.set_cuda_graphs(bool(graphs))
-        intra.set_cuda_graphs(bool(graphs))
+        # the I-frame (1 frame in 32) stays eager here: its captured programs (192-channel activations) would add
+        # ~4 GB of private graph pool per worker, and 8 workers x (DMC + IntraNoAR) pools overflow the 180 GB
+        intra.set_cuda_graphs(bool(graphs) and os.environ.get("VCM_BENCH_INTRA_GRAPHS", "0") == "1")
         workers.append(dict(dmc=dmc, intra=intra, stream=torch.cuda.Stream(dev), bits=0,
                             host_out=torch.empty((gop, H, W, 3), dtype=torch.uint8).pin_memory()))
     return workers
