@@ -568,3 +568,21 @@ def test_cuda_graphs_follow_a_weight_reload():
         got = chain(dmc)
         for (b0, r0), (b1, r1) in zip(want, got):
             assert b0 == b1 and torch.equal(r0, r1)
+
+
+@pytest.mark.timeout(300)
+def test_gop_pipeline_propagates_a_coder_error():
+    """A failure in the host-coder stage must surface as the exception, not as a hang: the entropy thread
+    drains the bounded symbol queue so the encoder thread can finish (pipeline.py)."""
+    from oracle import fixture
+    from vcm_ts_b200.pipeline import GopPipeline
+    dev = "cuda:0"
+    enc, dec = _models("bf16"), _models("bf16")
+    fr = fixture.fixture_frames(128, 192, 6, seed=17).to(dev)
+
+    def boom(host):
+        raise RuntimeError("coder failed")
+    enc[0].encode_symbols = boom
+    pipe = GopPipeline(enc, dec, dev)
+    with pytest.raises(RuntimeError, match="coder failed"):
+        pipe.code_gop([fr[t:t + 1] for t in range(6)], 128, 192, 1.0, 1.0, 1.0)
