@@ -262,8 +262,8 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     mbar_init(&rfull[1], 1);
     if (G.tma_epi) {
       prefetch_tmap(&tmY);
-      if (P.flags & VCM_CONV_OUT2) prefetch_tmap(&tmY2);
-      if (P.flags & (VCM_CONV_RES | VCM_CONV_RES_SCALE)) prefetch_tmap(&tmR);
+      if (G.tma_epi == 1 && (P.flags & VCM_CONV_OUT2)) prefetch_tmap(&tmY2);
+      if (G.tma_epi == 1 && (P.flags & (VCM_CONV_RES | VCM_CONV_RES_SCALE))) prefetch_tmap(&tmR);
     }
     fence_barrier_init();
   }
@@ -368,7 +368,28 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     const int q = warp & 3;   // TMEM lane quarter this warp may access
     const uint32_t stage = smem_u32(smem + G.epi_base) + (uint32_t)((warp - 4) * EPI_STAGE_FLOATS * 4);
     pdl_wait();   // residuals / SE scales are read and outputs written only after the predecessor finished
-    if (G.tma_epi) {
+    if (G.tma_epi == 2) {
+      // split-bf16 parity mode (mh == 1): fp32 tiles through TMA stores, one staging buffer per warpgroup
+      const uint32_t obuf = smem_u32(smem + G.epi_base) + (uint32_t)(g * EPI_TMA_TILE_BYTES);
+      const bool leader = (q == 0 && lane == 0);
+      int local = 0;
+      for (int item = blockIdx.x; item < G.num_items; item += gridDim.x, ++local) {
+        if ((local & 1) != g) continue;
+        const int ab = local % G.nacc;
+        const uint32_t acc_phase = (uint32_t)(local / G.nacc) & 1u;
+        const int nt = item % G.n_tiles, sp = item / G.n_tiles;
+        const int n = sp / sp_tiles, rem = sp - n * sp_tiles;
+        const int ox0 = (rem % G.tiles_x) * HTW, oy0 = (rem / G.tiles_x) * HTH;
+        const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(ab * G.nsacc * G.bn);
+        if (g == 0)
+          epilogue_warp_tma_f32<1>(P, &tmY, obuf, leader, G.bn, G.nsacc, n, oy0, ox0, nt * G.bn, taddr, q, lane,
+                                   &tfull[ab], acc_phase, &tempty[ab], bias_smem);
+        else
+          epilogue_warp_tma_f32<2>(P, &tmY, obuf, leader, G.bn, G.nsacc, n, oy0, ox0, nt * G.bn, taddr, q, lane,
+                                   &tfull[ab], acc_phase, &tempty[ab], bias_smem);
+      }
+      if (leader) tma_store_wait_all();
+    } else if (G.tma_epi) {
       // this warpgroup's k-th tile: item local = 2 * (k / mh) + g, half h = k % mh
       EpiTma E;
       E.tmY = &tmY; E.tmY2 = &tmY2; E.tmR = &tmR;
@@ -502,7 +523,13 @@ int vcm_conv_halo_launch(const vcm_conv_desc* d, const ConvParams& P, const void
   G.tma_epi = (!no_tma_epi && !G.split && G.scalar_epi == 0 && (G.bn == 64 || G.bn == 32) && P.Cout % G.bn == 0 &&
                !(P.flags & (VCM_CONV_PIXEL_SHUFFLE | VCM_CONV_RES2)) &&
                !((P.flags & VCM_CONV_OUT2) && (P.flags & (VCM_CONV_RES | VCM_CONV_RES_SCALE)))) ? 1 : 0;
-  const int epi_bytes = G.tma_epi ? EPI_TMA_BYTES : EPI_STAGE_BYTES;
+  if (!no_tma_epi && G.split && d->out_dtype == VCM_F32 && P.Cout % 32 == 0 && G.bn % 32 == 0 &&
+      !(P.flags & (VCM_CONV_PIXEL_SHUFFLE | VCM_CONV_RES2 | VCM_CONV_OUT2)) && P.out_cs % 4 == 0 &&
+      ((uintptr_t)P.y & 15) == 0 &&
+      (!(P.flags & (VCM_CONV_RES | VCM_CONV_RES_SCALE)) || (P.res_cs % 4 == 0 && ((uintptr_t)P.res & 15) == 0)) &&
+      (!(P.flags & VCM_CONV_RES_SCALE) || ((uintptr_t)P.res_scale & 15) == 0))
+    G.tma_epi = 2;   // fp32 sub-tiles of 32 channels (epilogue_warp_tma_f32)
+  const int epi_bytes = G.tma_epi == 1 ? EPI_TMA_BYTES : EPI_STAGE_BYTES;
   const int budget = SMEM_LIMIT - 1024 - 512 - bias_bytes - epi_bytes;   // alignment slack, barriers, bias, staging
 
   auto a_stage = [&](int mh) { return (G.split ? 3 : 1) * round_up(G.hw * (HTH * mh + P.K - 1) * chunk * 2, 1024); };
@@ -585,7 +612,19 @@ int vcm_conv_halo_launch(const vcm_conv_desc* d, const ConvParams& P, const void
   memset(&tmY, 0, sizeof(tmY));
   memset(&tmY2, 0, sizeof(tmY2));
   memset(&tmR, 0, sizeof(tmR));
-  if (G.tma_epi) {
+  if (G.tma_epi == 2) {
+    cuuint64_t dims[4] = {(cuuint64_t)P.Cout, (cuuint64_t)P.Wo, (cuuint64_t)P.Ho, (cuuint64_t)P.N};
+    cuuint64_t strides[3] = {(cuuint64_t)P.out_cs * 4, (cuuint64_t)P.Wo * P.out_cs * 4,
+                             (cuuint64_t)P.Ho * P.Wo * P.out_cs * 4};
+    cuuint32_t box[4] = {32, (cuuint32_t)HTW, (cuuint32_t)HTH, 1};
+    cuuint32_t estr[4] = {1, 1, 1, 1};
+    if (enc(&tmY, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, P.y, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+            CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+            CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS) {
+      vcm_set_error("vcm_conv_halo_launch: cuTensorMapEncodeTiled(fp32 output) failed");
+      return 1;
+    }
+  } else if (G.tma_epi) {
     auto out_map = [&](CUtensorMap* tm, const void* base, int cs) -> bool {
       cuuint64_t dims[4] = {(cuuint64_t)P.Cout, (cuuint64_t)P.Wo, (cuuint64_t)P.Ho, (cuuint64_t)P.N};
       cuuint64_t strides[3] = {(cuuint64_t)cs * 2, (cuuint64_t)P.Wo * cs * 2, (cuuint64_t)P.Ho * P.Wo * cs * 2};

@@ -396,6 +396,80 @@ __device__ __forceinline__ void epilogue_warp_tma(const ConvParams& P, EpiTma& E
   }
 }
 
+// fp32 variant for the split-bf16 parity mode: the item owns `nsum` accumulators of bn columns each; the tile is
+// written as bn / 32 sub-tiles of [128 px][32 ch] fp32 (128-byte rows, 128B swizzle), one TMA store each, through
+// ONE 16 KB staging buffer per warpgroup (the leader waits for the previous store's shared-memory reads).  The
+// residual is read straight from global memory (a thread's 32 channels are one contiguous 128-byte run).
+// Same float operations in the same order as epilogue_thread_scalar / conv_epilogue_store.
+template <int BAR>
+__device__ __forceinline__ void epilogue_warp_tma_f32(const ConvParams& P, const CUtensorMap* tmY, uint32_t obuf,
+                                                      bool leader, int bn, int nsum, int n, int oy0, int ox0,
+                                                      int cbase, uint32_t taddr, int wq, int lane, uint64_t* wait,
+                                                      uint32_t parity, uint64_t* release, uint32_t bias_smem) {
+  const bool has_res = P.flags & (VCM_CONV_RES | VCM_CONV_RES_SCALE);
+  const float slope = (P.flags & VCM_CONV_POST_ACT) ? P.post_slope : 1.0f;
+  const int m = wq * 32 + lane;
+  const int oy = oy0 + m / 8, ox = ox0 + m % 8;          // 8 x 16 tile (HTW = 8)
+  const bool valid = oy < P.Ho && ox < P.Wo;
+  const uint32_t row = (uint32_t)m * 128u;
+  const uint32_t sw = (uint32_t)(m & 7);
+  const size_t pix = ((size_t)n * P.Ho + (size_t)(valid ? oy : 0)) * (size_t)P.Wo + (size_t)(valid ? ox : 0);
+  const float* rp = reinterpret_cast<const float*>(P.res) + pix * (size_t)P.res_cs + cbase;
+  if (wait) {
+    mbar_wait(wait, parity);
+    tc_fence_after();
+  }
+  const int halves = bn / 32;
+  for (int half = 0; half < halves; ++half) {
+    float4 r[8];
+    if (has_res && valid) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) r[j] = __ldg(reinterpret_cast<const float4*>(rp + 32 * half + 4 * j));
+    }
+    float v[32];
+    tmem_load_block<32>(taddr + (uint32_t)(32 * half), v);
+    for (int a = 1; a < nsum; ++a) {
+      float u[32];
+      tmem_load_block<32>(taddr + (uint32_t)(a * bn + 32 * half), u);
+#pragma unroll
+      for (int i = 0; i < 32; ++i) v[i] = __fadd_rn(v[i], u[i]);
+    }
+    if (half == halves - 1 && release) {
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(release);
+    }
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const float4 b = lds128(bias_smem + (uint32_t)(cbase + 32 * half + 4 * j) * 4u);
+      float w0 = leaky01(v[4 * j] + b.x, slope), w1 = leaky01(v[4 * j + 1] + b.y, slope);
+      float w2 = leaky01(v[4 * j + 2] + b.z, slope), w3 = leaky01(v[4 * j + 3] + b.w, slope);
+      if (has_res && valid) {
+        if (P.flags & VCM_CONV_RES) {
+          w0 = r[j].x + w0; w1 = r[j].y + w1; w2 = r[j].z + w2; w3 = r[j].w + w3;
+        } else {
+          const float4 sc = __ldg(reinterpret_cast<const float4*>(P.res_scale + (size_t)n * P.Cout + cbase + 32 * half + 4 * j));
+          w0 = w0 + __fmul_rn(r[j].x, sc.x); w1 = w1 + __fmul_rn(r[j].y, sc.y);
+          w2 = w2 + __fmul_rn(r[j].z, sc.z); w3 = w3 + __fmul_rn(r[j].w, sc.w);
+        }
+      }
+      v[4 * j] = w0; v[4 * j + 1] = w1; v[4 * j + 2] = w2; v[4 * j + 3] = w3;
+    }
+    // the previous sub-tile's store must have finished reading the staging buffer
+    if (leader) tma_store_wait_read();
+    named_bar_sync(BAR, 128);
+#pragma unroll
+    for (int j = 0; j < 8; ++j)
+      sts128(obuf + row + (((uint32_t)j ^ sw) << 4), v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+    fence_proxy_async();
+    named_bar_sync(BAR, 128);
+    if (leader) {
+      tma_store_4d(tmY, obuf, cbase + 32 * half, ox0, oy0, n);
+      tma_store_commit();
+    }
+  }
+}
+
 // ------------------------------------------------------------------------------- scalar path
 // thread = pixel (oy, ox); loops over the bn columns of the slab
 // nsum > 1 (split-bf16 parity mode): the item owns nsum accumulators of bn columns each ([0] = correction
