@@ -47,6 +47,9 @@ class _Staging:
         self.device, self.depth = device, depth
         self.bufs, self.gen = {}, {}
         self.pin = device.type == "cuda"
+        # blocking event waits: the waiting thread sleeps instead of spinning, which matters when 8 ranks x 8
+        # coding threads share 32 logical CPUs with the rANS coder (VCM_B200_BLOCKING_SYNC=0: spin)
+        self.blocking = os.environ.get("VCM_B200_BLOCKING_SYNC", "1") == "1"
 
     def _buf(self, key, shape, dtype):
         b = self.bufs.get(key)
@@ -63,7 +66,7 @@ class _Staging:
             b.copy_(t, non_blocking=True)
             outs.append(b)
         if self.pin:
-            ev = torch.cuda.Event()
+            ev = torch.cuda.Event(blocking=self.blocking)
             ev.record(torch.cuda.current_stream(self.device))
             ev.synchronize()
         return outs
