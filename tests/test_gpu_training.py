@@ -104,19 +104,23 @@ def test_conv_function_gradients(precision, case):
     tg = TrainGraph(m, rt)
     g = torch.Generator().manual_seed(11)
     x = torch.randn((2, Cin, 24, 40), generator=g).to(dev).requires_grad_(True)
-    y = tg.conv("c", x, stride=stride, post=post, out_dtype=torch.float32)
-    go = torch.randn(y.shape, generator=g).to(dev)
-    gx, gw, gb = torch.autograd.grad(y, (x, m.c.weight, m.c.bias), go)
     # bf16 precision: the reference sees the same bf16-rounded operands, otherwise activation-mask flips of
-    # near-zero outputs (a factor 1/slope in the gradient) dominate the comparison
+    # near-zero outputs (a factor 1/slope in the gradient) dominate the comparison.  The reference runs in
+    # fp64: cuDNN's fp32 algorithm choice (Winograd: ~1e-5 absolute error) is not a usable reference for the
+    # sign of outputs near zero, and the output gradient is zeroed where |y| < 1e-4 for the same reason.
     rnd = (lambda t: t.bfloat16().float()) if precision == "bf16" else (lambda t: t)
-    x2 = rnd(x.detach()).clone().requires_grad_(True)
-    w2 = rnd(m.c.weight.detach()).clone().requires_grad_(True)
-    b2 = m.c.bias.detach().clone().requires_grad_(True)
+    x2 = rnd(x.detach()).double().requires_grad_(True)
+    w2 = rnd(m.c.weight.detach()).double().requires_grad_(True)
+    b2 = m.c.bias.detach().double().requires_grad_(True)
     y2 = F.conv2d(x2, w2, b2, stride, K // 2)
+    go = torch.randn(y2.shape, generator=g).to(dev)
     if post is not None:
+        go = go * (y2.detach().abs() > 1e-4)
         y2 = F.leaky_relu(y2, post)
-    gx2, gw2, gb2 = torch.autograd.grad(y2, (x2, w2, b2), go)
+    gx2, gw2, gb2 = torch.autograd.grad(y2, (x2, w2, b2), go.double())
+    y = tg.conv("c", x, stride=stride, post=post, out_dtype=torch.float32)
+    gx, gw, gb = torch.autograd.grad(y, (x, m.c.weight, m.c.bias), go)
+    y2, gx2, gw2, gb2 = (t.detach().float() for t in (y2, gx2, gw2, gb2))
     rel = lambda a, b: ((a.float() - b).norm() / b.norm()).item()   # noqa: E731
     tol = 3e-2 if precision == "bf16" else 2e-5
     errs = dict(y=rel(y, y2), gx=rel(gx, gx2), gw=rel(gw, gw2), gb=rel(gb, gb2))
