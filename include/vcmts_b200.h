@@ -253,6 +253,19 @@ int vcm_factorized_bits(const void* z_hat, const float* fparams, float* partial,
 /* sum((a-b)^2) per sample over NCHW fp32 tensors (video_model.py:544-545 mse / me_mse)      */
 int vcm_sq_err_sum(const float* a, const float* b, float* partial, float* out, int32_t N,
                    int64_t per_sample, void* stream);
+/* Allocation-free variant of vcm_sq_err_sum.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture,
+ * tight serving loops, harnesses that forbid it).  Same kernels and summation order as
+ * vcm_sq_err_sum (results are bit-identical), but the partial sums live in a 32 KiB
+ * `static __device__` array inside the library (held by every GPU that loads it, until exit)
+ * instead of caller scratch; the call itself allocates nothing.
+ * Limit: N * ceil(per_sample / 8192) <= 8192 partial sums (64 Mi elements in all, e.g. ten padded
+ * 1080p RGB frames); larger requests return 1 with a message in vcm_last_error().
+ * All calls on one device share the array: calls that overlap on the GPU (different streams) race.
+ * The first call on each device looks the array's address up (cudaGetSymbolAddress); make it
+ * outside any stream capture.                                                                 */
+int vcm_sq_err_sum_noalloc(const float* a, const float* b, float* out, int32_t N,
+                           int64_t per_sample, void* stream);
 
 /* ---- host entropy coder (CPU, GIL-free; bitstream identical to the reference) ----------
  * replaces MLCodec_rans BufferedRansEncoder / RansDecoder

@@ -80,6 +80,7 @@ _PROTOS = {
     "vcm_latent_bits": (c_int, [_P, _P, _P, _P, c_int32, c_int64, c_int32, _P]),
     "vcm_factorized_bits": (c_int, [_P, _P, _P, _P, c_int32, c_int64, c_int32, c_int32, c_int32, _P]),
     "vcm_sq_err_sum": (c_int, [_P, _P, _P, _P, c_int32, c_int64, _P]),
+    "vcm_sq_err_sum_noalloc": (c_int, [_P, _P, _P, c_int32, c_int64, _P]),
     "vcm_cdf_tables_new": (_P, [_P, _P, _P, c_int32, c_int32]),
     "vcm_cdf_tables_free": (None, [_P]),
     "vcm_rans_enc_new": (_P, []),

@@ -412,3 +412,51 @@ extern "C" int vcm_sq_err_sum(const float* a, const float* b, float* partial, fl
   VCM_CHECK_LAUNCH();
   return 0;
 }
+
+// ---- allocation-free variant of vcm_sq_err_sum ------------------------------------------
+// No counterpart in the reference: added for callers that
+// may not call cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid it).
+// The partial sums of the two-stage reduction live in a file-scope device array instead of a
+// caller-supplied buffer.  Every GPU that loads the library holds the 32 KiB until exit; all calls
+// on one device share it, so calls that overlap on the GPU (different streams) race.  Nothing has to
+// start at zero: every slot the second stage reads is written by the first stage of the same call.
+constexpr int NOALLOC_MAX_PARTIALS = 8192;   // N * ceil(per_sample / RED_CHUNK) <= 8192, i.e. 64 Mi elements
+static __device__ __align__(256) float g_noalloc_partial[NOALLOC_MAX_PARTIALS];
+
+extern "C" int vcm_sq_err_sum_noalloc(const float* a, const float* b, float* out, int32_t N,
+                                      int64_t per_sample, void* stream) {
+  VCM_CHECK_ARG(a && b && out && N > 0 && per_sample > 0, "bad argument");
+  const int64_t nblk64 = (per_sample + RED_CHUNK - 1) / RED_CHUNK;
+  if (nblk64 * N > NOALLOC_MAX_PARTIALS) {
+    vcm_set_error("%s: N * ceil(per_sample / %d) = %lld partial sums exceed the built-in scratch of %d "
+                  "(use vcm_sq_err_sum with caller scratch)", __func__, RED_CHUNK, (long long)(nblk64 * N),
+                  NOALLOC_MAX_PARTIALS);
+    return 1;
+  }
+  // device address of the scratch array, looked up once per device with that device current (the
+  // array's name is only a host-side handle here); idempotent, so racing first calls are harmless
+  constexpr int kMaxDev = 64;
+  static float* scratch_ptr[kMaxDev] = {nullptr};
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess || dev < 0 || dev >= kMaxDev) {
+    vcm_set_error("%s: cudaGetDevice: %s (device %d)", __func__, cudaGetErrorString(e), dev);
+    return 1;
+  }
+  float* partial = scratch_ptr[dev];
+  if (!partial) {
+    e = cudaGetSymbolAddress((void**)&partial, g_noalloc_partial);
+    if (e != cudaSuccess || !partial) {
+      vcm_set_error("%s: cudaGetSymbolAddress: %s", __func__, cudaGetErrorString(e));
+      return 1;
+    }
+    scratch_ptr[dev] = partial;
+  }
+  const int nblk = (int)nblk64;
+  cudaStream_t s = (cudaStream_t)stream;
+  sq_err_kernel<<<dim3(nblk, N), 256, 0, s>>>(a, b, partial, per_sample, nblk);
+  VCM_CHECK_LAUNCH();
+  final_sum_kernel<<<N, 32, 0, s>>>(partial, out, nblk);
+  VCM_CHECK_LAUNCH();
+  return 0;
+}
