@@ -20,6 +20,9 @@ int vcm_umma_rate(int32_t N, int32_t iters, long long* out, void* stream);
 /* same, with the A operand starting `start_row` 128-byte rows into the buffer and 8-row groups sbo_bytes apart */
 int vcm_umma_rate2(int32_t N, int32_t iters, int32_t start_row, int32_t sbo_bytes, long long* out,
                    void* stream);
+/* same, rotating over `nacc` accumulators of N TMEM columns each (nacc * N <= 512): issue rate vs the latency
+ * of a dependent accumulate */
+int vcm_umma_rate3(int32_t N, int32_t iters, int32_t nacc, long long* out, void* stream);
 /* TMA box-shape throughput probe: all SMs stream {64 ch, bw, bh} boxes of an NHWC bf16 [H][W][64] image
  * through a `stages`-deep ring (each box as nsplit TMA ops); out[0] = cycles of CTA 0, out[1] = its boxes */
 int vcm_tma_probe(const void* img, int32_t H, int32_t W, int32_t bw, int32_t bh, int32_t stages,

@@ -34,6 +34,11 @@ SHAPES = {
     "c64_64_8": (3, 1, 64, 64, 136, 240, True, False),
     "c128_128_q2": (3, 1, 128, 128, 272, 480, False, False),
     "c384_288_16": (3, 1, 384, 288, 68, 120, False, False),
+    "c64_32_full": (3, 1, 64, 32, 1088, 1920, False, False),
+    "c32_32_full": (3, 1, 32, 32, 1088, 1920, False, False),
+    "c16_64_full": (3, 1, 16, 64, 1088, 1920, False, False),
+    "c64_64_half_nores": (3, 1, 64, 64, 544, 960, False, False),
+    "c32_64_half": (3, 1, 32, 64, 544, 960, False, False),
 }
 
 

@@ -12,4 +12,13 @@ for N in (16, 32, 64, 128, 256):
         c = out[0].item() / 1024
         res[f"N{N}_start{start}_sbo{sbo}"] = c
         print(f"N={N:4d} start_row={start:2d} sbo={sbo:5d}: {c:7.1f} cycles/MMA -> {128*N*16*2/c:7.0f} FLOP/cycle/SM")
+for N in (16, 32, 64, 128, 256):
+    for nacc in (1, 2, 4, 8):
+        if nacc * N > 512:
+            continue
+        L.vcm_umma_rate3(N, 1024, nacc, out.data_ptr(), None)
+        torch.cuda.synchronize()
+        c = out[0].item() / 1024
+        res[f"N{N}_nacc{nacc}"] = c
+        print(f"N={N:4d} accumulators={nacc}: {c:7.1f} cycles/MMA -> {128*N*16*2/c:7.0f} FLOP/cycle/SM")
 json.dump(res, open("gpurun_out/umma_rate.json", "w"), indent=1)

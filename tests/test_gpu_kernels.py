@@ -274,11 +274,26 @@ TC_CASES = [
     (3, 1, 64, 64, 35, 29, 1, None, False, False, False, False, 0.01),
     (3, 1, 128, 64, 70, 90, 1, 0.1, False, True, False, False, None),     # streamed weights, 256-pixel items
     (1, 1, 64, 128, 33, 47, 1, None, False, True, False, False, None),    # Cout 128 as two 64-channel N tiles on a small image
+    # row-stacked engine (conv_rows.cu): Cout 64 -> 2 output rows per MMA, Cout 32 -> 4; ragged last strip
+    (3, 1, 64, 64, 304, 512, 1, 0.01, False, True, False, False, None),
+    (3, 1, 64, 64, 300, 480, 1, None, False, False, False, False, 0.01),
+    (3, 1, 64, 32, 304, 512, 2, 0.01, False, True, True, False, None),
+    (3, 1, 32, 32, 300, 460, 2, None, False, False, False, False, 0.1),
+    (3, 1, 16, 64, 304, 500, 1, 0.1, False, True, False, False, None),
+    (3, 1, 32, 64, 298, 640, 1, None, False, False, False, False, None),
 ]
 
 
+@pytest.fixture()
+def rows_engine_small_images():
+    """conv_rows.cu takes images at least 1024 wide by default; the test shapes are smaller."""
+    os.environ["VCM_TC_ROWS_MIN_W"] = "448"
+    yield
+    os.environ.pop("VCM_TC_ROWS_MIN_W", None)
+
+
 @pytest.mark.parametrize("case", TC_CASES)
-def test_conv_tcgen05_engine(B16, case):
+def test_conv_tcgen05_engine(B16, case, rows_engine_small_images):
     K, stride, Cin, Cout, H, W, N, post, ps, use_res, use_scale, use_res2, slope2 = case
     import ctypes
     from vcm_ts_b200 import _lib
@@ -315,6 +330,43 @@ def test_conv_tcgen05_engine(B16, case):
     if out2 is not None:
         w2 = F.leaky_relu(want, slope2)
         assert bool(((nchw(out2) - w2).abs() <= 0.01 * w2.abs() + 0.02).all())
+
+
+def test_conv_rows_engine_is_taken_and_equals_the_halo_engine(B16, rows_engine_small_images):
+    """3x3 64->64 (+ residual) on a large image runs on conv_rows_kernel (torch profiler kernel names); with
+    VCM_TC_NO_ROWS=1 the halo engine takes it.  Same products, fp32 accumulation in another order: the bf16
+    outputs may differ by one rounding step on a few values, never more."""
+    from torch.profiler import ProfilerActivity, profile
+    g = torch.Generator(device="cpu").manual_seed(5)
+    dev, bf = "cuda:0", torch.bfloat16
+    N, C, H, W = 1, 64, 304, 640
+    x = torch.randn((N, C, H, W), generator=g).to(dev).to(bf)
+    w = (torch.randn((C, C, 3, 3), generator=g) / 24).to(dev)
+    b = torch.randn((C,), generator=g).to(dev)
+    res = torch.randn((N, C, H, W), generator=g).to(dev).to(bf)
+    pc = B16.pack_conv(w, b)
+    xv, rv = view_of(x.float(), dtype=bf), view_of(res.float(), dtype=bf)
+
+    def run():
+        with profile(activities=[ProfilerActivity.CUDA]) as prof:
+            out = B16.conv(xv, pc, post=0.01, res=rv)
+            torch.cuda.synchronize()
+        return nchw(out), [e.key for e in prof.key_averages()]
+
+    os.environ.pop("VCM_TC_NO_ROWS", None)
+    got, names = run()
+    assert any("conv_rows_kernel" in k for k in names), names
+    os.environ["VCM_TC_NO_ROWS"] = "1"
+    try:
+        halo, names2 = run()
+    finally:
+        os.environ.pop("VCM_TC_NO_ROWS", None)
+    assert any("conv_halo_kernel" in k for k in names2) and not any("conv_rows_kernel" in k for k in names2), names2
+    diff = (got - halo).abs()
+    assert bool((diff <= 0.0079 * halo.abs() + 1e-6).all()), diff.max().item()      # one bf16 ulp
+    assert float((diff > 0).float().mean()) < 0.02
+    want = ref_conv(x.float(), w.to(bf).float(), b, 1, None, 0.01, False, res.float(), None, None)
+    assert bool(((got - want).abs() <= 0.01 * want.abs() + 0.02).all())
 
 
 def test_conv_tcgen05_unaligned_views_take_scalar_epilogue(B16):
@@ -613,6 +665,8 @@ FULL_CASES = [
     (3, 1, 128, 64, None, False),
     (7, 1, 32, 64, 0.0, False),
     (3, 2, 67, 64, 0.1, False),
+    (3, 1, 64, 32, 0.01, True),      # row-stacked engine, 4 output rows per MMA (UNet conv1)
+    (3, 1, 32, 32, None, False),
 ]
 
 

@@ -9,7 +9,7 @@ from ctypes import (POINTER, Structure, c_char_p, c_float, c_int, c_int16, c_int
                     c_uint8, c_void_p)
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-SO = os.path.join(HERE, "libvcmts_b200.so")
+SO = os.environ.get("VCM_B200_SO") or os.path.join(HERE, "libvcmts_b200.so")   # override: A/B runs of two builds
 
 F32, BF16 = 0, 1
 CONV_PRE_ACT, CONV_POST_ACT, CONV_PIXEL_SHUFFLE = 1, 2, 4

@@ -11,6 +11,7 @@ _PROTOS = {
     "vcm_umma_probe": (c_int, [c_int32, c_int32, c_int32, _P, _P]),
     "vcm_umma_rate": (c_int, [c_int32, c_int32, _P, _P]),
     "vcm_umma_rate2": (c_int, [c_int32, c_int32, c_int32, c_int32, _P, _P]),
+    "vcm_umma_rate3": (c_int, [c_int32, c_int32, c_int32, _P, _P]),
     "vcm_tma_probe": (c_int, [_P, c_int32, c_int32, c_int32, c_int32, c_int32, c_int32, _P, _P]),
     "vcm_umma_acc_probe": (c_int, [_P, _P, _P, _P]),
 }

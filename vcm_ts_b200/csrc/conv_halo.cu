@@ -90,7 +90,9 @@ __device__ __forceinline__ void mma_role(const HaloGeom& G, const HaloBars& B, u
       if (elect_one()) {
         const uint64_t adesc0 = make_smem_desc(a_smem + (uint32_t)as * (uint32_t)G.a_stage_bytes, HW * ROWB, LAYOUT);
         const uint64_t bch = bdesc0 + (uint64_t)((uint32_t)ch * bslot16);
-#pragma unroll
+        // 7x7 with 32-channel chunks: the filter-row loop stays a loop (measured 465 -> 451 us for 32->64 at
+        // 1088x1920; with 64-channel chunks the unrolled form was the faster one, 513 vs 535 us for 64->32)
+#pragma unroll(K <= 3 || CHUNK == 64 ? K : 1)
         for (int ky = 0; ky < K; ++ky) {
 #pragma unroll
           for (int kx = 0; kx < K; ++kx) {
@@ -177,7 +179,7 @@ __device__ __forceinline__ void mma_role_split(const HaloGeom& G, const HaloBars
         const uint64_t adesc0 = make_smem_desc(a_smem + (uint32_t)as * (uint32_t)G.a_stage_bytes, HW * ROWB, LAYOUT);
         for (int pj = 2; pj >= 0; --pj) {
           const uint64_t bch = bdesc0 + (uint64_t)((uint32_t)ch * bslot16 + (uint32_t)pj * bpart16);
-#pragma unroll
+#pragma unroll(K <= 3 ? K : 1)
           for (int ky = 0; ky < K; ++ky) {
 #pragma unroll
             for (int kx = 0; kx < K; ++kx) {
@@ -381,12 +383,8 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         const int n = sp / sp_tiles, rem = sp - n * sp_tiles;
         const int ox0 = (rem % G.tiles_x) * HTW, oy0 = (rem / G.tiles_x) * HTH;
         const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(ab * G.nsacc * G.bn);
-        if (g == 0)
-          epilogue_warp_tma_f32<1>(P, &tmY, obuf, leader, G.bn, G.nsacc, n, oy0, ox0, nt * G.bn, taddr, q, lane,
-                                   &tfull[ab], acc_phase, &tempty[ab], bias_smem);
-        else
-          epilogue_warp_tma_f32<2>(P, &tmY, obuf, leader, G.bn, G.nsacc, n, oy0, ox0, nt * G.bn, taddr, q, lane,
-                                   &tfull[ab], acc_phase, &tempty[ab], bias_smem);
+        epilogue_warp_tma_f32(1 + g, P, &tmY, obuf, leader, G.bn, G.nsacc, n, oy0, ox0, nt * G.bn, taddr, q, lane,
+                              &tfull[ab], acc_phase, &tempty[ab], bias_smem);
       }
       if (leader) tma_store_wait_all();
     } else if (G.tma_epi) {
@@ -398,6 +396,7 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       E.rfull = &rfull[g];
       E.rphase = 0;
       E.leader = (q == 0 && lane == 0);
+      E.bar = 1 + g;
       const bool has_res = P.flags & (VCM_CONV_RES | VCM_CONV_RES_SCALE);
       auto tile = [&](int k, int& item, int& h, int& n, int& oy0, int& ox0, int& cb) -> bool {
         const int loc = 2 * (k / G.mh) + g;
@@ -425,14 +424,11 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         const int ab = loc % G.nacc;
         const uint32_t acc_phase = (uint32_t)(loc / G.nacc) & 1u;
         const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)((ab * G.mh + h) * G.bn);
-#define EPI_TMA(BAR, BN)                                                                                        \
-  epilogue_warp_tma<BAR, BN>(P, E, n, oy0, ox0, cb, taddr, q, lane, h == 0 ? &tfull[ab] : nullptr, acc_phase,     \
-                             h == G.mh - 1 ? &tempty[ab] : nullptr, bias_smem, ok2, n2, oy2, ox2, cb2)
-        if (G.bn == 64) {
-          if (g == 0) EPI_TMA(1, 64); else EPI_TMA(2, 64);
-        } else {
-          if (g == 0) EPI_TMA(1, 32); else EPI_TMA(2, 32);
-        }
+#define EPI_TMA(BN)                                                                                             \
+  epilogue_warp_tma<BN>(P, E, n, oy0, ox0, cb, taddr, q, lane, h == 0 ? &tfull[ab] : nullptr, acc_phase,          \
+                        h == G.mh - 1 ? &tempty[ab] : nullptr, bias_smem, ok2, n2, oy2, ox2, cb2)
+        if (G.bn == 64) EPI_TMA(64);
+        else EPI_TMA(32);
 #undef EPI_TMA
         ok = ok2; item = item2; h = h2; n = n2; oy0 = oy2; ox0 = ox2; cb = cb2;
       }
@@ -489,6 +485,10 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
 int vcm_conv_halo_launch(const vcm_conv_desc* d, const ConvParams& P, const void* x, const void* w_umma,
                          cudaStream_t stream) {
   if (P.stride != 1) return 3;
+  {   // narrow 3x3 layers on large images: output rows stacked along N (conv_rows.cu)
+    const int rc = vcm_conv_rows_launch(d, P, x, w_umma, stream);
+    if (rc != 3) return rc;
+  }
   EncodeTiledFn enc = get_encode_fn();
   if (!enc) {
     vcm_set_error("vcm_conv_halo_launch: cuTensorMapEncodeTiled unavailable");

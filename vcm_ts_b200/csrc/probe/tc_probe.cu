@@ -98,7 +98,7 @@ extern "C" int vcm_umma_probe(int32_t start_row, int32_t sbo_bytes, int32_t use_
 // ---- MMA issue-rate probe: `iters` back-to-back 128 x N x 16 bf16 MMAs on fixed smem operands, one
 // commit at the end; out[0] = SM cycles from first issue to completion, out[1] = iters.
 namespace {
-__global__ void __launch_bounds__(128, 1) umma_rate_kernel(int N, int iters, int start_row, int sbo,
+__global__ void __launch_bounds__(128, 1) umma_rate_kernel(int N, int iters, int start_row, int sbo, int nacc,
                                                            long long* __restrict__ out) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
@@ -122,8 +122,19 @@ __global__ void __launch_bounds__(128, 1) umma_rate_kernel(int N, int iters, int
     const uint64_t bdesc = make_smem_desc(smem_u32(sB), 1024u, 2u);
     const uint32_t idesc = make_idesc_bf16(128, N);
     const long long t0 = clock64();
-    for (int i = 0; i < iters; ++i) umma_bf16(tmem_base + (uint32_t)((i & 1) * 256), adesc + (uint64_t)(2 * (i & 3)),
-                                              bdesc + (uint64_t)(2 * (i & 3)), idesc, 1u);
+    if (nacc <= 0) {
+      for (int i = 0; i < iters; ++i) umma_bf16(tmem_base + (uint32_t)((i & 1) * 256), adesc + (uint64_t)(2 * (i & 3)),
+                                                bdesc + (uint64_t)(2 * (i & 3)), idesc, 1u);
+    } else {
+      // rotate over `nacc` accumulators of N columns each: separates the issue rate from the latency of a
+      // dependent accumulate into the same TMEM columns
+      int a = 0;
+      for (int i = 0; i < iters; ++i) {
+        umma_bf16(tmem_base + (uint32_t)(a * N), adesc + (uint64_t)(2 * (i & 3)), bdesc + (uint64_t)(2 * (i & 3)),
+                  idesc, 1u);
+        if (++a == nacc) a = 0;
+      }
+    }
     umma_commit(bar);
     mbar_wait(bar, 0);
     const long long t1 = clock64();
@@ -154,7 +165,17 @@ extern "C" int vcm_umma_rate2(int32_t N, int32_t iters, int32_t start_row, int32
     cudaFuncSetAttribute(umma_rate_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes);
     attr_set = true;
   }
-  umma_rate_kernel<<<1, 128, smem_bytes, (cudaStream_t)stream>>>(N, iters, start_row, sbo_bytes, out);
+  umma_rate_kernel<<<1, 128, smem_bytes, (cudaStream_t)stream>>>(N, iters, start_row, sbo_bytes, 0, out);
+  VCM_CHECK_LAUNCH();
+  return 0;
+}
+
+extern "C" int vcm_umma_rate3(int32_t N, int32_t iters, int32_t nacc, long long* out, void* stream) {
+  VCM_CHECK_ARG(out && N >= 16 && N <= 256 && N % 16 == 0 && iters > 0 && nacc >= 1 && nacc * N <= 512,
+                "bad argument");
+  const int smem_bytes = (384 + 256) * 128 + 64 + 1024;
+  cudaFuncSetAttribute(umma_rate_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes);
+  umma_rate_kernel<<<1, 128, smem_bytes, (cudaStream_t)stream>>>(N, iters, 0, 1024, nacc, out);
   VCM_CHECK_LAUNCH();
   return 0;
 }

@@ -297,6 +297,7 @@ struct EpiTma {
   uint64_t* rfull;           // residual tile landed
   uint32_t rphase;
   bool leader;               // the one thread of the warpgroup that issues TMA operations
+  int bar;                   // named barrier of this warpgroup (1 or 2)
 };
 
 template <int BN>
@@ -310,7 +311,7 @@ __device__ __forceinline__ void epi_tma_prefetch_res(const EpiTma& E, int c, int
 // The 64 channels are processed as two halves of 32 to keep the register footprint small.  OUT2 (activated
 // twin) is only taken together with "no residual": the twin tile then uses the idle residual buffer.
 // BN = 64 (128-byte rows, 128B swizzle) or 32 (64-byte rows, 64B swizzle: chunk ^= (row >> 1) & 3).
-template <int BAR, int BN>
+template <int BN>
 __device__ __forceinline__ void epilogue_warp_tma(const ConvParams& P, EpiTma& E, int n, int oy0, int ox0, int cbase,
                                                   uint32_t taddr, int wq, int lane, uint64_t* wait, uint32_t parity,
                                                   uint64_t* release, uint32_t bias_smem, bool has_next, int nn,
@@ -323,7 +324,7 @@ __device__ __forceinline__ void epilogue_warp_tma(const ConvParams& P, EpiTma& E
   const uint32_t sw = BN == 64 ? (uint32_t)(m & 7) : (uint32_t)((m >> 1) & 3);
   // the previous tile's stores must have finished reading the staging tiles before they are overwritten
   if (E.leader) tma_store_wait_read();
-  named_bar_sync(BAR, 128);
+  named_bar_sync(E.bar, 128);
   if (wait) {
     mbar_wait(wait, parity);
     tc_fence_after();
@@ -332,7 +333,9 @@ __device__ __forceinline__ void epilogue_warp_tma(const ConvParams& P, EpiTma& E
     mbar_wait(E.rfull, E.rphase);
     E.rphase ^= 1u;
   }
-#pragma unroll
+  // not unrolled: one copy of the 32-channel body keeps the hot loop of the epilogue warps small (the
+  // instruction cache is shared with the MMA-issuing thread's long unrolled sequence)
+#pragma unroll 1
   for (int half = 0; half < BN / 32; ++half) {
     float v[32];
     tmem_load_block<32>(taddr + (uint32_t)(32 * half), v);
@@ -387,7 +390,7 @@ __device__ __forceinline__ void epilogue_warp_tma(const ConvParams& P, EpiTma& E
     }
   }
   fence_proxy_async();
-  named_bar_sync(BAR, 128);        // tiles complete; everybody is done reading the residual tile
+  named_bar_sync(E.bar, 128);        // tiles complete; everybody is done reading the residual tile
   if (E.leader) {
     tma_store_4d(E.tmY, E.obuf, cbase, ox0, oy0, n);
     if (twin) tma_store_4d(E.tmY2, E.rbuf, cbase, ox0, oy0, n);
@@ -401,8 +404,7 @@ __device__ __forceinline__ void epilogue_warp_tma(const ConvParams& P, EpiTma& E
 // ONE 16 KB staging buffer per warpgroup (the leader waits for the previous store's shared-memory reads).  The
 // residual is read straight from global memory (a thread's 32 channels are one contiguous 128-byte run).
 // Same float operations in the same order as epilogue_thread_scalar / conv_epilogue_store.
-template <int BAR>
-__device__ __forceinline__ void epilogue_warp_tma_f32(const ConvParams& P, const CUtensorMap* tmY, uint32_t obuf,
+__device__ __forceinline__ void epilogue_warp_tma_f32(int bar, const ConvParams& P, const CUtensorMap* tmY, uint32_t obuf,
                                                       bool leader, int bn, int nsum, int n, int oy0, int ox0,
                                                       int cbase, uint32_t taddr, int wq, int lane, uint64_t* wait,
                                                       uint32_t parity, uint64_t* release, uint32_t bias_smem) {
@@ -457,12 +459,12 @@ __device__ __forceinline__ void epilogue_warp_tma_f32(const ConvParams& P, const
     }
     // the previous sub-tile's store must have finished reading the staging buffer
     if (leader) tma_store_wait_read();
-    named_bar_sync(BAR, 128);
+    named_bar_sync(bar, 128);
 #pragma unroll
     for (int j = 0; j < 8; ++j)
       sts128(obuf + row + (((uint32_t)j ^ sw) << 4), v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
     fence_proxy_async();
-    named_bar_sync(BAR, 128);
+    named_bar_sync(bar, 128);
     if (leader) {
       tma_store_4d(tmY, obuf, cbase + 32 * half, ox0, oy0, n);
       tma_store_commit();

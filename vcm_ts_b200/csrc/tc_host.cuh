@@ -108,3 +108,6 @@ inline int tc_epilogue_bw(const vcm_conv_desc* d, int bn) {
 struct ConvParams;
 int vcm_conv_halo_launch(const vcm_conv_desc* d, const ConvParams& P, const void* x, const void* w_umma,
                          cudaStream_t stream);
+// row-stacked 3x3 engine for Cout = 64 / 32 (conv_rows.cu); same return convention
+int vcm_conv_rows_launch(const vcm_conv_desc* d, const ConvParams& P, const void* x, const void* w_umma,
+                         cudaStream_t stream);
