@@ -247,8 +247,8 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   uint64_t* bempty = bfull + H_MAX_B;
   uint64_t* tfull = bempty + H_MAX_B;
   uint64_t* tempty = tfull + H_MAX_ACC;
-  uint64_t* rfull = tempty + H_MAX_ACC;      // [2]: residual tile of epilogue warpgroup g has landed
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(rfull + 2);
+  uint64_t* rfull = tempty + H_MAX_ACC;      // [2][2]: residual tile b of epilogue warpgroup g has landed
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(rfull + 4);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int sp_tiles = G.tiles_x * G.tiles_y;
@@ -260,8 +260,7 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     for (int s = 0; s < H_MAX_A; ++s) { mbar_init(&afull[s], 1); mbar_init(&aempty[s], 1); }
     for (int s = 0; s < H_MAX_B; ++s) { mbar_init(&bfull[s], 1); mbar_init(&bempty[s], 1); }
     for (int a = 0; a < H_MAX_ACC; ++a) { mbar_init(&tfull[a], 1); mbar_init(&tempty[a], 4); }
-    mbar_init(&rfull[0], 1);
-    mbar_init(&rfull[1], 1);
+    for (int r = 0; r < 4; ++r) mbar_init(&rfull[r], 1);
     if (G.tma_epi) {
       prefetch_tmap(&tmY);
       if (G.tma_epi == 1 && (P.flags & VCM_CONV_OUT2)) prefetch_tmap(&tmY2);
@@ -392,16 +391,15 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       EpiTma E;
       E.tmY = &tmY; E.tmY2 = &tmY2; E.tmR = &tmR;
       E.obuf = smem_u32(smem + G.epi_base) + (uint32_t)(g * 2 * EPI_TMA_TILE_BYTES);
-      E.rbuf = E.obuf + (uint32_t)EPI_TMA_TILE_BYTES;
-      E.rfull = &rfull[g];
-      E.rphase = 0;
+      E.rfull = &rfull[2 * g];
+      E.k = 0;
       E.leader = (q == 0 && lane == 0);
       E.bar = 1 + g;
       const bool has_res = P.flags & (VCM_CONV_RES | VCM_CONV_RES_SCALE);
-      auto tile = [&](int k, int& item, int& h, int& n, int& oy0, int& ox0, int& cb) -> bool {
+      auto tile = [&](int k, int& h, int& n, int& oy0, int& ox0, int& cb) -> bool {
         const int loc = 2 * (k / G.mh) + g;
         h = k % G.mh;
-        item = blockIdx.x + loc * gridDim.x;
+        const int item = blockIdx.x + loc * gridDim.x;
         if (item >= G.num_items) return false;
         const int nt = item % G.n_tiles, sp = item / G.n_tiles;
         n = sp / sp_tiles;
@@ -411,15 +409,14 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         cb = nt * G.bn;
         return true;
       };
-      int item, h, n, oy0, ox0, cb;
-      bool ok = tile(0, item, h, n, oy0, ox0, cb);
-      if (ok && has_res && E.leader) {
-        if (G.bn == 64) epi_tma_prefetch_res<64>(E, cb, ox0, oy0, n);
-        else epi_tma_prefetch_res<32>(E, cb, ox0, oy0, n);
+      int h, n, oy0, ox0, cb;
+      if (has_res && E.leader && tile(0, h, n, oy0, ox0, cb)) {
+        if (G.bn == 64) epi_tma_prefetch_res<64>(E, 0, cb, ox0, oy0, n);
+        else epi_tma_prefetch_res<32>(E, 0, cb, ox0, oy0, n);
       }
-      for (int k = 0; ok; ++k) {
-        int item2, h2, n2, oy2, ox2, cb2;
-        const bool ok2 = tile(k + 1, item2, h2, n2, oy2, ox2, cb2);
+      for (int k = 0; tile(k, h, n, oy0, ox0, cb); ++k) {
+        int h2, n2, oy2, ox2, cb2;
+        const bool ok2 = has_res && tile(k + 1, h2, n2, oy2, ox2, cb2);   // whose residual is requested next
         const int loc = 2 * (k / G.mh) + g;
         const int ab = loc % G.nacc;
         const uint32_t acc_phase = (uint32_t)(loc / G.nacc) & 1u;
@@ -430,7 +427,6 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         if (G.bn == 64) EPI_TMA(64);
         else EPI_TMA(32);
 #undef EPI_TMA
-        ok = ok2; item = item2; h = h2; n = n2; oy0 = oy2; ox0 = ox2; cb = cb2;
       }
       if (E.leader) tma_store_wait_all();
     } else {
@@ -529,10 +525,10 @@ int vcm_conv_halo_launch(const vcm_conv_desc* d, const ConvParams& P, const void
       (!(P.flags & (VCM_CONV_RES | VCM_CONV_RES_SCALE)) || (P.res_cs % 4 == 0 && ((uintptr_t)P.res & 15) == 0)) &&
       (!(P.flags & VCM_CONV_RES_SCALE) || ((uintptr_t)P.res_scale & 15) == 0))
     G.tma_epi = 2;   // fp32 sub-tiles of 32 channels (epilogue_warp_tma_f32)
+  auto a_stage = [&](int mh) { return (G.split ? 3 : 1) * round_up(G.hw * (HTH * mh + P.K - 1) * chunk * 2, 1024); };
   const int epi_bytes = G.tma_epi == 1 ? EPI_TMA_BYTES : EPI_STAGE_BYTES;
   const int budget = SMEM_LIMIT - 1024 - 512 - bias_bytes - epi_bytes;   // alignment slack, barriers, bias, staging
 
-  auto a_stage = [&](int mh) { return (G.split ? 3 : 1) * round_up(G.hw * (HTH * mh + P.K - 1) * chunk * 2, 1024); };
   // resident weights if they leave room for >= 3 activation stages
   G.resident = (G.n_tiles == 1) && (slabs * G.b_slot_bytes + (G.split ? 2 : 3) * a_stage(1) <= budget);
   if (G.resident) {

@@ -40,7 +40,6 @@ struct RowsGeom {
   int b_base, b_slot_bytes;
   int strips, groups, num_items;      // groups = Ho / R per strip; items = N * strips * groups
   int epi_base, bar_base, bias_base;
-  int epi_stride;      // bytes between the two epilogue warpgroups' staging areas (output tile [+ residual / twin tile])
   int prefetch_rows;   // L2 prefetch distance of the row producer, in input rows (0 = off)
 };
 
@@ -147,8 +146,8 @@ conv_rows_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   uint64_t* bfull = aempty + R_MAX_SLOTS;    // [1]
   uint64_t* tfull = bfull + 1;
   uint64_t* tempty = tfull + R_NACC;
-  uint64_t* rfull = tempty + R_NACC;         // [2]
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(rfull + 2);
+  uint64_t* rfull = tempty + R_NACC;         // [2][2]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(rfull + 4);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   // this CTA's contiguous run of items
@@ -164,8 +163,7 @@ conv_rows_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     for (int s = 0; s < R_MAX_SLOTS; ++s) { mbar_init(&afull[s], 1); mbar_init(&aempty[s], 1); }
     mbar_init(bfull, 1);
     for (int a = 0; a < R_NACC; ++a) { mbar_init(&tfull[a], 1); mbar_init(&tempty[a], 4); }
-    mbar_init(&rfull[0], 1);
-    mbar_init(&rfull[1], 1);
+    for (int r = 0; r < 4; ++r) mbar_init(&rfull[r], 1);
     fence_barrier_init();
   }
   if (warp == 1) tmem_alloc(tmem_slot, 512u);
@@ -229,10 +227,9 @@ conv_rows_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     pdl_wait();
     EpiTma E;
     E.tmY = &tmY; E.tmY2 = &tmY2; E.tmR = &tmR;
-    E.obuf = smem_u32(smem + G.epi_base) + (uint32_t)(g * G.epi_stride);
-    E.rbuf = E.obuf + (uint32_t)EPI_TMA_TILE_BYTES;
-    E.rfull = &rfull[g];
-    E.rphase = 0;
+    E.obuf = smem_u32(smem + G.epi_base) + (uint32_t)(g * 2 * EPI_TMA_TILE_BYTES);
+    E.rfull = &rfull[2 * g];
+    E.k = 0;
     E.leader = (q == 0 && lane == 0);
     E.bar = 1 + g;
     const bool has_res = P.flags & (VCM_CONV_RES | VCM_CONV_RES_SCALE);
@@ -250,7 +247,7 @@ conv_rows_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     int h, n, oy0, ox0;
     bool ok = tile(0, h, n, oy0, ox0);
     if (ok && has_res && E.leader) {
-      epi_tma_prefetch_res<128 / R>(E, 0, ox0, oy0, n);
+      epi_tma_prefetch_res<128 / R>(E, 0, 0, ox0, oy0, n);
     }
     for (int k = 0; ok; ++k) {
       int h2, n2, oy2, ox2;
@@ -317,11 +314,7 @@ int vcm_conv_rows_launch(const vcm_conv_desc* d, const ConvParams& P, const void
   G.b_slot_bytes = G.bn * chunk * 2;                 // 64x64: 8 KB, 32x64: 4 KB, ... multiples of the swizzle atom
   if (G.b_slot_bytes % (8 * chunk * 2)) return 3;
   const int bias_bytes = 512;
-  // staging per epilogue warpgroup: the output tile, plus a second tile only when a residual is prefetched or a
-  // twin output is written
-  const bool two_tiles = P.flags & (VCM_CONV_RES | VCM_CONV_RES_SCALE | VCM_CONV_OUT2);
-  G.epi_stride = (two_tiles ? 2 : 1) * EPI_TMA_TILE_BYTES;
-  const int epi_bytes = 2 * G.epi_stride;
+  const int epi_bytes = EPI_TMA_BYTES;   // two staging tiles per epilogue warpgroup
   const char* pf_env = getenv("VCM_ROWS_PF");
   G.prefetch_rows = pf_env ? atoi(pf_env) : 0;
   const int budget = SMEM_LIMIT - 1024 - 512 - bias_bytes - epi_bytes - 9 * G.b_slot_bytes;

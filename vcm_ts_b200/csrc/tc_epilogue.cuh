@@ -293,23 +293,33 @@ constexpr int EPI_TMA_BYTES = 4 * EPI_TMA_TILE_BYTES;         // per warpgroup: 
 
 struct EpiTma {
   const CUtensorMap *tmY, *tmY2, *tmR;
-  uint32_t obuf, rbuf;       // shared-window addresses of this warpgroup's output / residual (or twin) tiles
-  uint64_t* rfull;           // residual tile landed
-  uint32_t rphase;
+  uint32_t obuf;             // shared-window address of this warpgroup's TWO staging tiles (obuf, obuf + 16 KB)
+  uint64_t* rfull;           // [2] residual tile landed in staging tile b
+  int k;                     // tiles this warpgroup has finished (staging tile k & 1, barrier phase (k >> 1) & 1)
   bool leader;               // the one thread of the warpgroup that issues TMA operations
   int bar;                   // named barrier of this warpgroup (1 or 2)
 };
 
+// residual tile of this warpgroup's tile number `k` -> staging tile k & 1 (where the output is then formed)
 template <int BN>
-__device__ __forceinline__ void epi_tma_prefetch_res(const EpiTma& E, int c, int x0, int y0, int n) {
-  mbar_expect_tx(E.rfull, (uint32_t)(128 * BN * 2));
-  tma_load_4d(E.rbuf, E.tmR, E.rfull, c, x0, y0, n);
+__device__ __forceinline__ void epi_tma_prefetch_res(const EpiTma& E, int k, int c, int x0, int y0, int n) {
+  const int b = k & 1;
+  mbar_expect_tx(&E.rfull[b], (uint32_t)(128 * BN * 2));
+  tma_load_4d(E.obuf + (uint32_t)(b * EPI_TMA_TILE_BYTES), E.tmR, &E.rfull[b], c, x0, y0, n);
 }
 
 // One warp's 32 pixels of a 128-pixel x 64-channel tile (wq = TMEM lane quarter = tile rows 32*wq ..).
-// next_*: the coordinates of this warpgroup's next tile (residual prefetch), has_next = false at the end.
-// The 64 channels are processed as two halves of 32 to keep the register footprint small.  OUT2 (activated
-// twin) is only taken together with "no residual": the twin tile then uses the idle residual buffer.
+// The warpgroup owns two staging tiles and alternates between them.  A residual tile is loaded by TMA INTO
+// the staging tile its output will be formed in and updated in place (each 16-byte chunk is read and
+// rewritten by the one thread that owns it), so the second tile buys lead time instead of holding a copy:
+// the residual of tile k + 1 is requested at the START of tile k, as soon as the store of tile k - 1 has
+// finished reading that buffer.  (Before: one output + one residual buffer, the request went out when the
+// next tile was about to start, and every tile waited a DRAM latency for it -- ncu: the wait on rfull was
+// the top stall of the 1x1 + residual convs, 164 -> 134 us at 1088x1920 once it had lead.)  Without a
+// residual the two tiles double-buffer the output, so nobody waits for the previous store to drain.
+// next_*: the coordinates of this warpgroup's NEXT tile (has_next = false at the end).
+// OUT2 (activated twin) is only taken together with "no residual": staging tile 0 = output, 1 = twin.
+// The 64 channels are processed as two halves of 32 to keep the register footprint small.
 // BN = 64 (128-byte rows, 128B swizzle) or 32 (64-byte rows, 64B swizzle: chunk ^= (row >> 1) & 3).
 template <int BN>
 __device__ __forceinline__ void epilogue_warp_tma(const ConvParams& P, EpiTma& E, int n, int oy0, int ox0, int cbase,
@@ -322,17 +332,25 @@ __device__ __forceinline__ void epilogue_warp_tma(const ConvParams& P, EpiTma& E
   const int m = wq * 32 + lane;                 // tile row = pixel
   const uint32_t row = (uint32_t)m * (uint32_t)(BN * 2);
   const uint32_t sw = BN == 64 ? (uint32_t)(m & 7) : (uint32_t)((m >> 1) & 3);
-  // the previous tile's stores must have finished reading the staging tiles before they are overwritten
-  if (E.leader) tma_store_wait_read();
-  named_bar_sync(E.bar, 128);
+  const int b = twin ? 0 : (E.k & 1);
+  const uint32_t obuf = E.obuf + (uint32_t)(b * EPI_TMA_TILE_BYTES);
+  const uint32_t tbuf = E.obuf + (uint32_t)EPI_TMA_TILE_BYTES;      // twin tile (twin mode only)
+  if (twin) {
+    // fixed buffers: the previous tile's stores must have finished reading them before they are overwritten
+    if (E.leader) tma_store_wait_read();
+    named_bar_sync(E.bar, 128);
+  } else if (has_res && E.leader) {
+    // staging tile 1 - b: its last store (tile k - 1) must be done reading before the next residual lands in
+    // it.  Staging tile b needs no check here: the same wait one tile ago covered its last store (tile k - 2),
+    // and that tile's closing barrier published it.
+    tma_store_wait_read();
+    if (has_next) epi_tma_prefetch_res<BN>(E, E.k + 1, ncbase, nox0, noy0, nn);
+  }
   if (wait) {
     mbar_wait(wait, parity);
     tc_fence_after();
   }
-  if (has_res) {
-    mbar_wait(E.rfull, E.rphase);
-    E.rphase ^= 1u;
-  }
+  if (has_res) mbar_wait(&E.rfull[b], (uint32_t)(E.k >> 1) & 1u);
   // not unrolled: one copy of the 32-channel body keeps the hot loop of the epilogue warps small (the
   // instruction cache is shared with the MMA-issuing thread's long unrolled sequence)
 #pragma unroll 1
@@ -346,11 +364,11 @@ __device__ __forceinline__ void epilogue_warp_tma(const ConvParams& P, EpiTma& E
     }
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
-      const float4 b = lds128(bias_smem + (uint32_t)(cbase + 32 * half + 4 * j) * 4u);
-      v[4 * j] = leaky01(v[4 * j] + b.x, slope);
-      v[4 * j + 1] = leaky01(v[4 * j + 1] + b.y, slope);
-      v[4 * j + 2] = leaky01(v[4 * j + 2] + b.z, slope);
-      v[4 * j + 3] = leaky01(v[4 * j + 3] + b.w, slope);
+      const float4 bb = lds128(bias_smem + (uint32_t)(cbase + 32 * half + 4 * j) * 4u);
+      v[4 * j] = leaky01(v[4 * j] + bb.x, slope);
+      v[4 * j + 1] = leaky01(v[4 * j + 1] + bb.y, slope);
+      v[4 * j + 2] = leaky01(v[4 * j + 2] + bb.z, slope);
+      v[4 * j + 3] = leaky01(v[4 * j + 3] + bb.w, slope);
     }
 #pragma unroll
     for (int j = 0; j < 4; ++j) {
@@ -359,7 +377,8 @@ __device__ __forceinline__ void epilogue_warp_tma(const ConvParams& P, EpiTma& E
         uint4 rr;
         asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];"
                      : "=r"(rr.x), "=r"(rr.y), "=r"(rr.z), "=r"(rr.w)
-                     : "r"(E.rbuf + row + chunk));
+                     : "r"(obuf + row + chunk)
+                     : "memory");
         float r[8];
         unpack8(rr, r);
         if (P.flags & VCM_CONV_RES) {
@@ -375,7 +394,7 @@ __device__ __forceinline__ void epilogue_warp_tma(const ConvParams& P, EpiTma& E
         }
       }
       const uint4 o = pack8(v + 8 * j);
-      asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(E.obuf + row + chunk), "r"(o.x), "r"(o.y),
+      asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(obuf + row + chunk), "r"(o.x), "r"(o.y),
                    "r"(o.z), "r"(o.w)
                    : "memory");
       if (twin) {
@@ -383,20 +402,23 @@ __device__ __forceinline__ void epilogue_warp_tma(const ConvParams& P, EpiTma& E
 #pragma unroll
         for (int i = 0; i < 8; ++i) t[i] = leaky01(v[8 * j + i], P.out2_slope);
         const uint4 o2 = pack8(t);
-        asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(E.rbuf + row + chunk), "r"(o2.x), "r"(o2.y),
+        asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(tbuf + row + chunk), "r"(o2.x), "r"(o2.y),
                      "r"(o2.z), "r"(o2.w)
                      : "memory");
       }
     }
   }
   fence_proxy_async();
-  named_bar_sync(E.bar, 128);        // tiles complete; everybody is done reading the residual tile
+  // plain output: the store of tile k - 1 (issued a whole tile ago) must be done reading staging tile 1 - b
+  // before tile k + 1 writes it; the barrier below publishes that
+  if (!twin && !has_res && E.leader) tma_store_wait_read();
+  named_bar_sync(E.bar, 128);        // the tile is complete in shared memory
   if (E.leader) {
-    tma_store_4d(E.tmY, E.obuf, cbase, ox0, oy0, n);
-    if (twin) tma_store_4d(E.tmY2, E.rbuf, cbase, ox0, oy0, n);
+    tma_store_4d(E.tmY, obuf, cbase, ox0, oy0, n);
+    if (twin) tma_store_4d(E.tmY2, tbuf, cbase, ox0, oy0, n);
     tma_store_commit();
-    if (has_res && has_next) epi_tma_prefetch_res<BN>(E, ncbase, nox0, noy0, nn);
   }
+  ++E.k;
 }
 
 // fp32 variant for the split-bf16 parity mode: the item owns `nsum` accumulators of bn columns each; the tile is
