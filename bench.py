@@ -561,7 +561,7 @@ def roofline_entry(rf, peaks, precision):
     use_tc = rf["tc_s"] > 0
     ach = (rf["tc_flop"] / rf["tc_s"] if use_tc else rf["all_flop"] / max(rf["all_s"], 1e-9)) / 1e12
     roof = {"bound": "tensor",
-            "kernel": "conv_halo_kernel / conv_tc_kernel (tcgen05 implicit GEMM, all launches of one P-frame)"
+            "kernel": "conv_halo_kernel / conv_rows_kernel / conv_tc_kernel (tcgen05 implicit GEMM, all launches of one P-frame)"
             if use_tc else "conv_simt_kernel",
             "achieved": ach, "peak": peak, "unit": "TFLOP/s", "frac": ach / peak,
             "peak_source": "MEASURED_PEAKS.json bf16_tflops_sustained" if peaks else "fallback 1400 (sustained)",
@@ -590,7 +590,7 @@ def roofline_entry(rf, peaks, precision):
         dom = {"shape": k0, "launches": v0[2], "ms_per_launch": v0[0] / v0[2],
                "achieved": v0[1] / max(v0[0], 1e-9) / 1e9, "unit": "TFLOP/s",
                "frac": v0[1] / max(v0[0], 1e-9) / 1e9 / peak, "traffic": None}
-        for name in ("ncu_conv64_halo_r02.json", "ncu_conv64_halo_r01.json"):
+        for name in ("ncu_conv64_rows_r02.json", "ncu_conv64_halo_r02.json", "ncu_conv64_halo_r01.json"):
             try:
                 prof = json.load(open(os.path.join(ROOT, "profiles", name)))[0]
                 mb = lambda key: float(next(v for k, v in prof.items() if k.startswith(key)))   # noqa: E731

@@ -39,6 +39,9 @@ SHAPES = {
     "c16_64_full": (3, 1, 16, 64, 1088, 1920, False, False),
     "c64_64_half_nores": (3, 1, 64, 64, 544, 960, False, False),
     "c32_64_half": (3, 1, 32, 64, 544, 960, False, False),
+    "k7_16_32_full": (7, 1, 16, 32, 1088, 1920, False, False),
+    "k7_32_16_full": (7, 1, 32, 16, 1088, 1920, False, False),
+    "c64_3_full": (3, 1, 64, 3, 1088, 1920, False, False),
 }
 
 

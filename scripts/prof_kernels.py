@@ -33,7 +33,13 @@ def conv(Bk, K, stride, Cin, Cout, H, W, res=False, dt=bf):
     torch.cuda.synchronize()
 
 
-conv(B, 3, 1, 64, 64, 1088, 1920, res=True)
+conv(B, 3, 1, 64, 64, 1088, 1920, res=True)        # conv_rows_kernel<64, 2> (2 output rows stacked along N)
+os.environ["VCM_TC_NO_ROWS"] = "1"
+conv(B, 3, 1, 64, 64, 1088, 1920, res=True)        # the same launch on conv_halo_kernel<64>
+os.environ.pop("VCM_TC_NO_ROWS")
+conv(B, 3, 1, 64, 32, 1088, 1920, res=True)        # conv_rows_kernel<64, 4>
+conv(B, 1, 1, 64, 64, 1088, 1920, res=True)        # 1x1 + residual: HBM-bound
+conv(B, 3, 1, 64, 64, 544, 960, res=True)
 conv(B, 3, 1, 128, 128, 272, 480, res=True)
 conv(B, 3, 1, 192, 192, 68, 120)
 conv(B, 7, 1, 32, 64, 1088, 1920)

@@ -274,6 +274,10 @@ TC_CASES = [
     (3, 1, 64, 64, 35, 29, 1, None, False, False, False, False, 0.01),
     (3, 1, 128, 64, 70, 90, 1, 0.1, False, True, False, False, None),     # streamed weights, 256-pixel items
     (1, 1, 64, 128, 33, 47, 1, None, False, True, False, False, None),    # Cout 128 as two 64-channel N tiles on a small image
+    # streamed weights, 256-pixel items, 3.6 items per CTA at the BASELINE 1/4-scale shape
+    (3, 1, 128, 128, 272, 480, 1, 0.01, False, True, False, False, None),
+    (3, 1, 128, 128, 272, 488, 1, None, False, False, False, False, None),
+    (3, 1, 64, 128, 272, 488, 1, 0.1, False, False, False, False, None),
     # row-stacked engine (conv_rows.cu): Cout 64 -> 2 output rows per MMA, Cout 32 -> 4; ragged last strip
     (3, 1, 64, 64, 304, 512, 1, 0.01, False, True, False, False, None),
     (3, 1, 64, 64, 300, 480, 1, None, False, False, False, False, 0.01),
@@ -281,6 +285,9 @@ TC_CASES = [
     (3, 1, 32, 32, 300, 460, 2, None, False, False, False, False, 0.1),
     (3, 1, 16, 64, 304, 500, 1, 0.1, False, True, False, False, None),
     (3, 1, 32, 64, 298, 640, 1, None, False, False, False, False, None),
+    # ... and its 7x7 forms (SpyNet conv1 / conv4): 4 resp. 8 output rows per MMA, 16-channel TMA tiles
+    (7, 1, 16, 32, 300, 460, 2, 0.0, False, False, False, False, None),
+    (7, 1, 32, 16, 304, 500, 4, 0.0, False, False, False, False, None),
 ]
 
 
@@ -332,16 +339,17 @@ def test_conv_tcgen05_engine(B16, case, rows_engine_small_images):
         assert bool(((nchw(out2) - w2).abs() <= 0.01 * w2.abs() + 0.02).all())
 
 
-def test_conv_rows_engine_is_taken_and_equals_the_halo_engine(B16, rows_engine_small_images):
+@pytest.mark.parametrize("shape", [(3, 64, 64, 1, 304, 640), (7, 32, 16, 4, 304, 512), (7, 16, 32, 2, 304, 512)])
+def test_conv_rows_engine_is_taken_and_equals_the_halo_engine(B16, rows_engine_small_images, shape):
     """3x3 64->64 (+ residual) on a large image runs on conv_rows_kernel (torch profiler kernel names); with
     VCM_TC_NO_ROWS=1 the halo engine takes it.  Same products, fp32 accumulation in another order: the bf16
-    outputs may differ by one rounding step on a few values, never more."""
+    outputs may differ by one rounding step on a few values, never more.  Same for the 7x7 forms."""
     from torch.profiler import ProfilerActivity, profile
     g = torch.Generator(device="cpu").manual_seed(5)
     dev, bf = "cuda:0", torch.bfloat16
-    N, C, H, W = 1, 64, 304, 640
-    x = torch.randn((N, C, H, W), generator=g).to(dev).to(bf)
-    w = (torch.randn((C, C, 3, 3), generator=g) / 24).to(dev)
+    K, Ci, C, N, H, W = shape
+    x = torch.randn((N, Ci, H, W), generator=g).to(dev).to(bf)
+    w = (torch.randn((C, Ci, K, K), generator=g) / (Ci * K * K) ** 0.5).to(dev)
     b = torch.randn((C,), generator=g).to(dev)
     res = torch.randn((N, C, H, W), generator=g).to(dev).to(bf)
     pc = B16.pack_conv(w, b)
@@ -599,11 +607,14 @@ SCALAR_TC_CASES = [
     (1, 64, 64, 8, True, False, 17, 30),       # mv_decoder subpel -> 2-channel flow
     (7, 8, 16, 32, False, False, 24, 40),      # SpyNet conv1, input padded 8 -> 16 (bf16 out)
     (3, 3, 16, 64, False, False, 32, 48),      # feature_adaptor_I, frame padded 3 -> 16 (bf16 out)
+    # row-stacked engine with the scalar epilogue (conv_rows.cu): 4 / 8 output rows per MMA
+    (3, 64, 64, 3, False, False, 304, 1000),   # recon_conv at a size the engine takes
+    (7, 16, 16, 2, False, True, 608, 1000),    # SpyNet conv5 + flow residual
 ]
 
 
 @pytest.mark.parametrize("case", SCALAR_TC_CASES)
-def test_conv_tcgen05_padded_and_fp32_out(B16, case):
+def test_conv_tcgen05_padded_and_fp32_out(B16, case, rows_engine_small_images):
     K, Cin, Cin_p, Cout, ps, use_res, H, W = case
     g = torch.Generator(device="cpu").manual_seed(200 + SCALAR_TC_CASES.index(case))
     dev, bf = "cuda:0", torch.bfloat16

@@ -391,6 +391,7 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       EpiTma E;
       E.tmY = &tmY; E.tmY2 = &tmY2; E.tmR = &tmR;
       E.obuf = smem_u32(smem + G.epi_base) + (uint32_t)(g * 2 * EPI_TMA_TILE_BYTES);
+      E.tile_bytes = (uint32_t)EPI_TMA_TILE_BYTES;
       E.rfull = &rfull[2 * g];
       E.k = 0;
       E.leader = (q == 0 && lane == 0);

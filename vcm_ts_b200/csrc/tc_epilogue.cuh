@@ -293,7 +293,8 @@ constexpr int EPI_TMA_BYTES = 4 * EPI_TMA_TILE_BYTES;         // per warpgroup: 
 
 struct EpiTma {
   const CUtensorMap *tmY, *tmY2, *tmR;
-  uint32_t obuf;             // shared-window address of this warpgroup's TWO staging tiles (obuf, obuf + 16 KB)
+  uint32_t obuf;             // shared-window address of this warpgroup's TWO staging tiles (obuf, obuf + tile_bytes)
+  uint32_t tile_bytes;       // distance between them (EPI_TMA_TILE_BYTES, or less for narrow tiles)
   uint64_t* rfull;           // [2] residual tile landed in staging tile b
   int k;                     // tiles this warpgroup has finished (staging tile k & 1, barrier phase (k >> 1) & 1)
   bool leader;               // the one thread of the warpgroup that issues TMA operations
@@ -305,7 +306,7 @@ template <int BN>
 __device__ __forceinline__ void epi_tma_prefetch_res(const EpiTma& E, int k, int c, int x0, int y0, int n) {
   const int b = k & 1;
   mbar_expect_tx(&E.rfull[b], (uint32_t)(128 * BN * 2));
-  tma_load_4d(E.obuf + (uint32_t)(b * EPI_TMA_TILE_BYTES), E.tmR, &E.rfull[b], c, x0, y0, n);
+  tma_load_4d(E.obuf + (uint32_t)b * E.tile_bytes, E.tmR, &E.rfull[b], c, x0, y0, n);
 }
 
 // One warp's 32 pixels of a 128-pixel x 64-channel tile (wq = TMEM lane quarter = tile rows 32*wq ..).
@@ -320,7 +321,8 @@ __device__ __forceinline__ void epi_tma_prefetch_res(const EpiTma& E, int k, int
 // next_*: the coordinates of this warpgroup's NEXT tile (has_next = false at the end).
 // OUT2 (activated twin) is only taken together with "no residual": staging tile 0 = output, 1 = twin.
 // The 64 channels are processed as two halves of 32 to keep the register footprint small.
-// BN = 64 (128-byte rows, 128B swizzle) or 32 (64-byte rows, 64B swizzle: chunk ^= (row >> 1) & 3).
+// BN = 64 (128-byte rows, 128B swizzle), 32 (64-byte rows, 64B swizzle: chunk ^= (row >> 1) & 3) or 16 (32-byte
+// rows, 32B swizzle: chunk ^= (row >> 2) & 1).
 template <int BN>
 __device__ __forceinline__ void epilogue_warp_tma(const ConvParams& P, EpiTma& E, int n, int oy0, int ox0, int cbase,
                                                   uint32_t taddr, int wq, int lane, uint64_t* wait, uint32_t parity,
@@ -331,10 +333,11 @@ __device__ __forceinline__ void epilogue_warp_tma(const ConvParams& P, EpiTma& E
   const float slope = (P.flags & VCM_CONV_POST_ACT) ? P.post_slope : 1.0f;
   const int m = wq * 32 + lane;                 // tile row = pixel
   const uint32_t row = (uint32_t)m * (uint32_t)(BN * 2);
-  const uint32_t sw = BN == 64 ? (uint32_t)(m & 7) : (uint32_t)((m >> 1) & 3);
+  const uint32_t sw = BN == 64 ? (uint32_t)(m & 7) : (BN == 32 ? (uint32_t)((m >> 1) & 3) : (uint32_t)((m >> 2) & 1));
+  constexpr int CB = BN < 32 ? BN : 32;         // channels per pass
   const int b = twin ? 0 : (E.k & 1);
-  const uint32_t obuf = E.obuf + (uint32_t)(b * EPI_TMA_TILE_BYTES);
-  const uint32_t tbuf = E.obuf + (uint32_t)EPI_TMA_TILE_BYTES;      // twin tile (twin mode only)
+  const uint32_t obuf = E.obuf + (uint32_t)b * E.tile_bytes;
+  const uint32_t tbuf = E.obuf + E.tile_bytes;      // twin tile (twin mode only)
   if (twin) {
     // fixed buffers: the previous tile's stores must have finished reading them before they are overwritten
     if (E.leader) tma_store_wait_read();
@@ -354,25 +357,25 @@ __device__ __forceinline__ void epilogue_warp_tma(const ConvParams& P, EpiTma& E
   // not unrolled: one copy of the 32-channel body keeps the hot loop of the epilogue warps small (the
   // instruction cache is shared with the MMA-issuing thread's long unrolled sequence)
 #pragma unroll 1
-  for (int half = 0; half < BN / 32; ++half) {
-    float v[32];
-    tmem_load_block<32>(taddr + (uint32_t)(32 * half), v);
-    if (half == BN / 32 - 1 && release) {      // last TMEM read of the tile
+  for (int half = 0; half < BN / CB; ++half) {
+    float v[CB];
+    tmem_load_block<CB>(taddr + (uint32_t)(CB * half), v);
+    if (half == BN / CB - 1 && release) {      // last TMEM read of the tile
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(release);
     }
 #pragma unroll
-    for (int j = 0; j < 8; ++j) {
-      const float4 bb = lds128(bias_smem + (uint32_t)(cbase + 32 * half + 4 * j) * 4u);
+    for (int j = 0; j < CB / 4; ++j) {
+      const float4 bb = lds128(bias_smem + (uint32_t)(cbase + CB * half + 4 * j) * 4u);
       v[4 * j] = leaky01(v[4 * j] + bb.x, slope);
       v[4 * j + 1] = leaky01(v[4 * j + 1] + bb.y, slope);
       v[4 * j + 2] = leaky01(v[4 * j + 2] + bb.z, slope);
       v[4 * j + 3] = leaky01(v[4 * j + 3] + bb.w, slope);
     }
 #pragma unroll
-    for (int j = 0; j < 4; ++j) {
-      const uint32_t chunk = ((uint32_t)(4 * half + j) ^ sw) << 4;
+    for (int j = 0; j < CB / 8; ++j) {
+      const uint32_t chunk = ((uint32_t)(CB / 8 * half + j) ^ sw) << 4;
       if (has_res) {
         uint4 rr;
         asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];"
@@ -385,7 +388,7 @@ __device__ __forceinline__ void epilogue_warp_tma(const ConvParams& P, EpiTma& E
 #pragma unroll
           for (int i = 0; i < 8; ++i) v[8 * j + i] = r[i] + v[8 * j + i];
         } else {
-          const float* sp = P.res_scale + (size_t)n * P.Cout + cbase + 32 * half + 8 * j;
+          const float* sp = P.res_scale + (size_t)n * P.Cout + cbase + CB * half + 8 * j;
           const float4 s0 = __ldg(reinterpret_cast<const float4*>(sp));
           const float4 s1 = __ldg(reinterpret_cast<const float4*>(sp + 4));
           const float sc[8] = {s0.x, s0.y, s0.z, s0.w, s1.x, s1.y, s1.z, s1.w};
