@@ -48,6 +48,7 @@ struct HaloGeom {
   int bn, cout_p, tmem_cols, scalar_epi;
   int nacc;   // TMEM accumulator ring depth (2 or 4): lets the MMA warp run ahead of both epilogue warpgroups
   int epi_base, bar_base, bias_base, epi_bw;
+  int scale_off;   // byte offset (from bias_base) of the shared-memory copy of res_scale, 0 = none
   int tma_epi;   // 64-channel bf16 tiles leave through a TMA store (tc_epilogue.cuh epilogue_warp_tma)
   uint32_t idesc;
 };
@@ -273,6 +274,10 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     float* bs_ = reinterpret_cast<float*>(smem + G.bias_base);
     const int nb = G.cout_p < EPI_BIAS_MAX ? G.cout_p : EPI_BIAS_MAX;
     for (int i = threadIdx.x; i < nb; i += blockDim.x) bs_[i] = i < P.Cout ? __ldg(P.bias + i) : 0.f;
+    if (G.scale_off) {   // SE scales of the residual (not under PDL: they are the predecessor's output)
+      float* sc_ = reinterpret_cast<float*>(smem + G.bias_base + G.scale_off);
+      for (int i = threadIdx.x; i < P.N * P.Cout; i += blockDim.x) sc_[i] = __ldg(P.res_scale + i);
+    }
   }
   tc_fence_before();
   __syncthreads();
@@ -392,6 +397,7 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       E.tmY = &tmY; E.tmY2 = &tmY2; E.tmR = &tmR;
       E.obuf = smem_u32(smem + G.epi_base) + (uint32_t)(g * 2 * EPI_TMA_TILE_BYTES);
       E.tile_bytes = (uint32_t)EPI_TMA_TILE_BYTES;
+      E.scale_smem = G.scale_off ? smem_u32(smem + G.bias_base + G.scale_off) : 0u;
       E.rfull = &rfull[2 * g];
       E.k = 0;
       E.leader = (q == 0 && lane == 0);
@@ -514,7 +520,11 @@ int vcm_conv_halo_launch(const vcm_conv_desc* d, const ConvParams& P, const void
   G.b_bytes = G.bn * chunk * 2;
   G.b_slot_bytes = round_up(G.b_bytes, 1024);
   const int slabs = G.ntaps * G.nchunks * (G.split ? 3 : 1);
-  const int bias_bytes = round_up((G.cout_p < EPI_BIAS_MAX ? G.cout_p : EPI_BIAS_MAX) * 4, 128);
+  int bias_bytes = round_up((G.cout_p < EPI_BIAS_MAX ? G.cout_p : EPI_BIAS_MAX) * 4, 128);
+  if ((P.flags & VCM_CONV_RES_SCALE) && !(P.flags & VCM_CONV_PDL) && P.N * P.Cout <= 2048) {
+    G.scale_off = bias_bytes;
+    bias_bytes += round_up(P.N * P.Cout * 4, 128);
+  }
   G.scalar_epi = tc_epilogue_mode(d, P);
   static const bool no_tma_epi = getenv("VCM_TC_NO_TMA_EPI") && getenv("VCM_TC_NO_TMA_EPI")[0] == '1';
   G.tma_epi = (!no_tma_epi && !G.split && G.scalar_epi == 0 && (G.bn == 64 || G.bn == 32) && P.Cout % G.bn == 0 &&

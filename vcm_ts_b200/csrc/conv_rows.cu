@@ -49,6 +49,7 @@ struct RowsGeom {
   int b_base, b_slot_bytes;
   int strips, groups, num_items;      // groups = Ho / R per strip; items = N * strips * groups
   int epi_base, bar_base, bias_base;
+  int scale_off;       // byte offset (from bias_base) of the shared-memory copy of res_scale, 0 = none
 };
 
 // item -> (n, strip, group); consecutive items walk DOWN a strip
@@ -181,6 +182,10 @@ conv_rows_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   {
     float* bs_ = reinterpret_cast<float*>(smem + G.bias_base);
     for (int i = threadIdx.x; i < G.bn; i += blockDim.x) bs_[i] = i < P.Cout ? __ldg(P.bias + i) : 0.f;
+    if (G.scale_off) {   // SE scales of the residual (not under PDL: they are the predecessor's output)
+      float* sc_ = reinterpret_cast<float*>(smem + G.bias_base + G.scale_off);
+      for (int i = threadIdx.x; i < P.N * P.Cout; i += blockDim.x) sc_[i] = __ldg(P.res_scale + i);
+    }
   }
   tc_fence_before();
   __syncthreads();
@@ -259,6 +264,7 @@ conv_rows_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     E.tmY = &tmY; E.tmY2 = &tmY2; E.tmR = &tmR;
     E.obuf = smem_u32(smem + G.epi_base) + (uint32_t)(g * 2 * G.tile_bytes);
     E.tile_bytes = (uint32_t)G.tile_bytes;
+    E.scale_smem = G.scale_off ? smem_u32(smem + G.bias_base + G.scale_off) : 0u;
     E.rfull = &rfull[2 * g];
     E.k = 0;
     E.leader = (q == 0 && lane == 0);
@@ -365,7 +371,11 @@ int vcm_conv_rows_launch(const vcm_conv_desc* d, const ConvParams& P, const void
   G.slot_bytes = round_up(G.a_bytes, 1024);
   G.b_slot_bytes = G.bn * chunk * 2;                 // 64x64: 8 KB ... 16x16: 512 B: multiples of the swizzle atom
   if (G.b_slot_bytes % (8 * chunk * 2)) return 3;
-  const int bias_bytes = 512;
+  int bias_bytes = 512;
+  if ((P.flags & VCM_CONV_RES_SCALE) && !(P.flags & VCM_CONV_PDL) && P.N * P.Cout <= 2048) {
+    G.scale_off = bias_bytes;
+    bias_bytes += round_up(P.N * P.Cout * 4, 128);
+  }
   G.tile_bytes = round_up(128 * G.bn * 2, 1024);
   const int epi_bytes = G.scalar_epi ? 0 : 4 * G.tile_bytes;   // two staging tiles per epilogue warpgroup
   const int budget = SMEM_LIMIT - 1024 - 512 - bias_bytes - epi_bytes - round_up(taps * G.b_slot_bytes, 1024);

@@ -296,6 +296,7 @@ struct EpiTma {
   uint32_t obuf;             // shared-window address of this warpgroup's TWO staging tiles (obuf, obuf + tile_bytes)
   uint32_t tile_bytes;       // distance between them (EPI_TMA_TILE_BYTES, or less for narrow tiles)
   uint64_t* rfull;           // [2] residual tile landed in staging tile b
+  uint32_t scale_smem;       // shared-window address of a copy of res_scale [N][Cout] (0: read it from global)
   int k;                     // tiles this warpgroup has finished (staging tile k & 1, barrier phase (k >> 1) & 1)
   bool leader;               // the one thread of the warpgroup that issues TMA operations
   int bar;                   // named barrier of this warpgroup (1 or 2)
@@ -388,9 +389,16 @@ __device__ __forceinline__ void epilogue_warp_tma(const ConvParams& P, EpiTma& E
 #pragma unroll
           for (int i = 0; i < 8; ++i) v[8 * j + i] = r[i] + v[8 * j + i];
         } else {
-          const float* sp = P.res_scale + (size_t)n * P.Cout + cbase + CB * half + 8 * j;
-          const float4 s0 = __ldg(reinterpret_cast<const float4*>(sp));
-          const float4 s1 = __ldg(reinterpret_cast<const float4*>(sp + 4));
+          // SE scales: from the shared-memory copy (16 dependent global loads per tile and thread otherwise)
+          const int so = n * P.Cout + cbase + CB * half + 8 * j;
+          float4 s0, s1;
+          if (E.scale_smem) {
+            s0 = lds128(E.scale_smem + (uint32_t)so * 4u);
+            s1 = lds128(E.scale_smem + (uint32_t)so * 4u + 16u);
+          } else {
+            s0 = __ldg(reinterpret_cast<const float4*>(P.res_scale + so));
+            s1 = __ldg(reinterpret_cast<const float4*>(P.res_scale + so + 4));
+          }
           const float sc[8] = {s0.x, s0.y, s0.z, s0.w, s1.x, s1.y, s1.z, s1.w};
 #pragma unroll
           for (int i = 0; i < 8; ++i) v[8 * j + i] = v[8 * j + i] + __fmul_rn(r[i], sc[i]);
