@@ -49,7 +49,9 @@ struct HaloGeom {
   int nacc;   // TMEM accumulator ring depth (2 or 4): lets the MMA warp run ahead of both epilogue warpgroups
   int epi_base, bar_base, bias_base, epi_bw;
   int scale_off;   // byte offset (from bias_base) of the shared-memory copy of res_scale, 0 = none
-  int tma_epi;   // 64-channel bf16 tiles leave through a TMA store (tc_epilogue.cuh epilogue_warp_tma)
+  int tma_epi;   // bf16 tiles leave through TMA stores (tc_epilogue.cuh epilogue_warp_tma)
+  int sw, nsub;  // tma_epi == 1: an N tile of bn columns leaves as nsub sub-tiles of sw (64 / 32) channels
+  int ps_q4;     // PixelShuffle through TMA: Cout / 4 (sub-tiles go to the strided positions of one sub-pixel phase), else 0
   uint32_t idesc;
 };
 
@@ -403,35 +405,52 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       E.leader = (q == 0 && lane == 0);
       E.bar = 1 + g;
       const bool has_res = P.flags & (VCM_CONV_RES | VCM_CONV_RES_SCALE);
-      auto tile = [&](int k, int& h, int& n, int& oy0, int& ox0, int& cb) -> bool {
-        const int loc = 2 * (k / G.mh) + g;
-        h = k % G.mh;
+      // this warpgroup's k-th tile: item local = 2 * (k / (mh * nsub)) + g, then (half h, column sub-tile)
+      const int per_item = G.mh * G.nsub;
+      // -> tensor-map coordinates (sx, sy, cs) of the tile, its first GEMM column cb and TMEM column offset tc
+      auto tile = [&](int k, int& n, int& sy, int& sx, int& cs, int& cb, int& tc, bool& first, bool& last) -> bool {
+        const int loc = 2 * (k / per_item) + g;
+        const int rem = k % per_item;
+        const int h = rem / G.nsub, sub = rem - h * G.nsub;
         const int item = blockIdx.x + loc * gridDim.x;
         if (item >= G.num_items) return false;
         const int nt = item % G.n_tiles, sp = item / G.n_tiles;
         n = sp / sp_tiles;
-        const int rem = sp - n * sp_tiles;
-        ox0 = (rem % G.tiles_x) * HTW;
-        oy0 = (rem / G.tiles_x) * (HTH * G.mh) + h * HTH;
-        cb = nt * G.bn;
+        const int r2 = sp - n * sp_tiles;
+        const int ox0 = (r2 % G.tiles_x) * HTW;
+        const int oy0 = (r2 / G.tiles_x) * (HTH * G.mh) + h * HTH;
+        cb = nt * G.bn + sub * G.sw;
+        tc = h * G.bn + sub * G.sw;
+        if (G.ps_q4) {     // GEMM column = phase * q4 + channel: phase (dy, dx) of the 2x upsampled image
+          const int pos = cb / G.ps_q4;
+          cs = cb - pos * G.ps_q4;
+          sx = 2 * ox0 + (pos & 1);
+          sy = 2 * oy0 + (pos >> 1);
+        } else {
+          cs = cb; sx = ox0; sy = oy0;
+        }
+        first = rem == 0;
+        last = rem == per_item - 1;
         return true;
       };
-      int h, n, oy0, ox0, cb;
-      if (has_res && E.leader && tile(0, h, n, oy0, ox0, cb)) {
-        if (G.bn == 64) epi_tma_prefetch_res<64>(E, 0, cb, ox0, oy0, n);
-        else epi_tma_prefetch_res<32>(E, 0, cb, ox0, oy0, n);
+      int n, sy, sx, cs, cb, tc;
+      bool first, last;
+      if (has_res && E.leader && tile(0, n, sy, sx, cs, cb, tc, first, last)) {
+        if (G.sw == 64) epi_tma_prefetch_res<64>(E, 0, cs, sx, sy, n);
+        else epi_tma_prefetch_res<32>(E, 0, cs, sx, sy, n);
       }
-      for (int k = 0; tile(k, h, n, oy0, ox0, cb); ++k) {
-        int h2, n2, oy2, ox2, cb2;
-        const bool ok2 = has_res && tile(k + 1, h2, n2, oy2, ox2, cb2);   // whose residual is requested next
-        const int loc = 2 * (k / G.mh) + g;
+      for (int k = 0; tile(k, n, sy, sx, cs, cb, tc, first, last); ++k) {
+        int n2, sy2, sx2, cs2, cb2, tc2;
+        bool f2, l2;
+        const bool ok2 = has_res && tile(k + 1, n2, sy2, sx2, cs2, cb2, tc2, f2, l2);   // whose residual is requested next
+        const int loc = 2 * (k / per_item) + g;
         const int ab = loc % G.nacc;
         const uint32_t acc_phase = (uint32_t)(loc / G.nacc) & 1u;
-        const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)((ab * G.mh + h) * G.bn);
+        const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(ab * G.mh * G.bn + tc);
 #define EPI_TMA(BN)                                                                                             \
-  epilogue_warp_tma<BN>(P, E, n, oy0, ox0, cb, taddr, q, lane, h == 0 ? &tfull[ab] : nullptr, acc_phase,          \
-                        h == G.mh - 1 ? &tempty[ab] : nullptr, bias_smem, ok2, n2, oy2, ox2, cb2)
-        if (G.bn == 64) EPI_TMA(64);
+  epilogue_warp_tma<BN>(P, E, n, sy, sx, cs, cb, taddr, q, lane, first ? &tfull[ab] : nullptr, acc_phase,         \
+                        last ? &tempty[ab] : nullptr, bias_smem, ok2, n2, sy2, sx2, cs2)
+        if (G.sw == 64) EPI_TMA(64);
         else EPI_TMA(32);
 #undef EPI_TMA
       }
@@ -527,9 +546,20 @@ int vcm_conv_halo_launch(const vcm_conv_desc* d, const ConvParams& P, const void
   }
   G.scalar_epi = tc_epilogue_mode(d, P);
   static const bool no_tma_epi = getenv("VCM_TC_NO_TMA_EPI") && getenv("VCM_TC_NO_TMA_EPI")[0] == '1';
-  G.tma_epi = (!no_tma_epi && !G.split && G.scalar_epi == 0 && (G.bn == 64 || G.bn == 32) && P.Cout % G.bn == 0 &&
-               !(P.flags & (VCM_CONV_PIXEL_SHUFFLE | VCM_CONV_RES2)) &&
+  // TMA-store epilogue: the N tile leaves as sub-tiles of 64 (or 32) channels.  PixelShuffle layers qualify when
+  // a sub-pixel phase (Cout / 4 GEMM columns) is a whole number of sub-tiles: a phase is then an ordinary tile
+  // of a tensor map that walks the 2x upsampled output with element strides 2.
+  G.sw = G.bn % 64 == 0 ? 64 : 32;
+  const bool ps = P.flags & VCM_CONV_PIXEL_SHUFFLE;
+  if (ps && (P.Cout / 4) % G.sw) G.sw = 32;
+  G.nsub = G.bn / G.sw;
+  static const bool no_wide_tma = getenv("VCM_TC_NO_WIDE_TMA_EPI") && getenv("VCM_TC_NO_WIDE_TMA_EPI")[0] == '1';
+  G.tma_epi = (!no_tma_epi && !G.split && G.scalar_epi == 0 && G.bn % G.sw == 0 && P.Cout % G.sw == 0 &&
+               G.cout_p == P.Cout && (!ps || ((P.Cout / 4) % G.sw == 0 && P.Cout % 4 == 0 && !(P.flags & VCM_CONV_RES_SCALE))) &&
+               (!no_wide_tma || (!ps && G.nsub == 1)) &&
+               !(P.flags & VCM_CONV_RES2) &&
                !((P.flags & VCM_CONV_OUT2) && (P.flags & (VCM_CONV_RES | VCM_CONV_RES_SCALE)))) ? 1 : 0;
+  G.ps_q4 = (G.tma_epi && ps) ? P.Cout / 4 : 0;
   if (!no_tma_epi && G.split && d->out_dtype == VCM_F32 && P.Cout % 32 == 0 && G.bn % 32 == 0 &&
       !(P.flags & (VCM_CONV_PIXEL_SHUFFLE | VCM_CONV_RES2 | VCM_CONV_OUT2)) && P.out_cs % 4 == 0 &&
       ((uintptr_t)P.y & 15) == 0 &&
@@ -633,12 +663,15 @@ int vcm_conv_halo_launch(const vcm_conv_desc* d, const ConvParams& P, const void
     }
   } else if (G.tma_epi) {
     auto out_map = [&](CUtensorMap* tm, const void* base, int cs) -> bool {
-      cuuint64_t dims[4] = {(cuuint64_t)P.Cout, (cuuint64_t)P.Wo, (cuuint64_t)P.Ho, (cuuint64_t)P.N};
-      cuuint64_t strides[3] = {(cuuint64_t)cs * 2, (cuuint64_t)P.Wo * cs * 2, (cuuint64_t)P.Ho * P.Wo * cs * 2};
-      cuuint32_t box[4] = {(cuuint32_t)G.bn, (cuuint32_t)HTW, (cuuint32_t)HTH, 1};
-      cuuint32_t estr[4] = {1, 1, 1, 1};
+      const int up = G.ps_q4 ? 2 : 1;                      // PixelShuffle: the 2x image, every other pixel per phase
+      const int ch = G.ps_q4 ? G.ps_q4 : P.Cout;
+      cuuint64_t dims[4] = {(cuuint64_t)ch, (cuuint64_t)(up * P.Wo), (cuuint64_t)(up * P.Ho), (cuuint64_t)P.N};
+      cuuint64_t strides[3] = {(cuuint64_t)cs * 2, (cuuint64_t)(up * P.Wo) * cs * 2,
+                               (cuuint64_t)(up * P.Ho) * (up * P.Wo) * cs * 2};
+      cuuint32_t box[4] = {(cuuint32_t)G.sw, (cuuint32_t)(up * HTW), (cuuint32_t)(up * HTH), 1};
+      cuuint32_t estr[4] = {1, (cuuint32_t)up, (cuuint32_t)up, 1};
       return enc(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(base), dims, strides, box, estr,
-                 CU_TENSOR_MAP_INTERLEAVE_NONE, G.bn == 64 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B,
+                 CU_TENSOR_MAP_INTERLEAVE_NONE, G.sw == 64 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B,
                  CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
     };
     bool ok = out_map(&tmY, P.y, P.out_cs);

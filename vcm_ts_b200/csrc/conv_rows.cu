@@ -291,7 +291,7 @@ conv_rows_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       const int ab = loc % R_NACC;
       const uint32_t acc_phase = (uint32_t)(loc / R_NACC) & 1u;
       const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(ab * 128 + h * BN);
-      epilogue_warp_tma<BN>(P, E, n, oy0, ox0, 0, taddr, q, lane, h == 0 ? &tfull[ab] : nullptr, acc_phase,
+      epilogue_warp_tma<BN>(P, E, n, oy0, ox0, 0, 0, taddr, q, lane, h == 0 ? &tfull[ab] : nullptr, acc_phase,
                             h == R - 1 ? &tempty[ab] : nullptr, bias_smem, ok2, n2, oy2, ox2, 0);
       ok = ok2; h = h2; n = n2; oy0 = oy2; ox0 = ox2;
     }

@@ -319,16 +319,18 @@ __device__ __forceinline__ void epi_tma_prefetch_res(const EpiTma& E, int k, int
 // next tile was about to start, and every tile waited a DRAM latency for it -- ncu: the wait on rfull was
 // the top stall of the 1x1 + residual convs, 164 -> 134 us at 1088x1920 once it had lead.)  Without a
 // residual the two tiles double-buffer the output, so nobody waits for the previous store to drain.
-// next_*: the coordinates of this warpgroup's NEXT tile (has_next = false at the end).
+// (ox0, oy0, cstore): tensor-map coordinates of the tile (output pixel and channel; PixelShuffle tiles go through a
+// map with element strides 2, see conv_halo.cu); cbase: first GEMM column (bias index).
+// next_*: the tensor-map coordinates of this warpgroup's NEXT tile (has_next = false at the end).
 // OUT2 (activated twin) is only taken together with "no residual": staging tile 0 = output, 1 = twin.
 // The 64 channels are processed as two halves of 32 to keep the register footprint small.
 // BN = 64 (128-byte rows, 128B swizzle), 32 (64-byte rows, 64B swizzle: chunk ^= (row >> 1) & 3) or 16 (32-byte
 // rows, 32B swizzle: chunk ^= (row >> 2) & 1).
 template <int BN>
-__device__ __forceinline__ void epilogue_warp_tma(const ConvParams& P, EpiTma& E, int n, int oy0, int ox0, int cbase,
-                                                  uint32_t taddr, int wq, int lane, uint64_t* wait, uint32_t parity,
-                                                  uint64_t* release, uint32_t bias_smem, bool has_next, int nn,
-                                                  int noy0, int nox0, int ncbase) {
+__device__ __forceinline__ void epilogue_warp_tma(const ConvParams& P, EpiTma& E, int n, int oy0, int ox0, int cstore,
+                                                  int cbase, uint32_t taddr, int wq, int lane, uint64_t* wait,
+                                                  uint32_t parity, uint64_t* release, uint32_t bias_smem,
+                                                  bool has_next, int nn, int noy0, int nox0, int ncbase) {
   const bool has_res = P.flags & (VCM_CONV_RES | VCM_CONV_RES_SCALE);
   const bool twin = P.flags & VCM_CONV_OUT2;
   const float slope = (P.flags & VCM_CONV_POST_ACT) ? P.post_slope : 1.0f;
@@ -390,7 +392,7 @@ __device__ __forceinline__ void epilogue_warp_tma(const ConvParams& P, EpiTma& E
           for (int i = 0; i < 8; ++i) v[8 * j + i] = r[i] + v[8 * j + i];
         } else {
           // SE scales: from the shared-memory copy (16 dependent global loads per tile and thread otherwise)
-          const int so = n * P.Cout + cbase + CB * half + 8 * j;
+          const int so = n * P.Cout + cstore + CB * half + 8 * j;
           float4 s0, s1;
           if (E.scale_smem) {
             s0 = lds128(E.scale_smem + (uint32_t)so * 4u);
@@ -425,8 +427,8 @@ __device__ __forceinline__ void epilogue_warp_tma(const ConvParams& P, EpiTma& E
   if (!twin && !has_res && E.leader) tma_store_wait_read();
   named_bar_sync(E.bar, 128);        // the tile is complete in shared memory
   if (E.leader) {
-    tma_store_4d(E.tmY, obuf, cbase, ox0, oy0, n);
-    if (twin) tma_store_4d(E.tmY2, tbuf, cbase, ox0, oy0, n);
+    tma_store_4d(E.tmY, obuf, cstore, ox0, oy0, n);
+    if (twin) tma_store_4d(E.tmY2, tbuf, cstore, ox0, oy0, n);
     tma_store_commit();
   }
   ++E.k;
