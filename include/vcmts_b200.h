@@ -52,6 +52,13 @@ extern "C" {
                                      Only set it when the packed weights were written by an EARLIER,
                                      completed launch (not by the kernel just before this one).           */
 
+#define VCM_CONV_SE_SUM 512       /* tensor-core engine, bf16: the SELayer mean (video_net.py:149-162 `avg_pool`)
+                                     fused into the conv that produces its input: y2 is then a float array
+                                     [vcm_conv2d_se_sum_rows(d)][Cout] that receives per-warp channel sums of
+                                     the bf16 outputs; vcm_se_scale_from_sums turns them into the scales.
+                                     Only where vcm_conv2d_se_sum_rows(d) > 0 (N = 1, whole tiles, Cout 64 / 32,
+                                     no OUT2); otherwise the launch fails.                               */
+
 typedef struct {
   int32_t N, H, W;        /* input batch / height / width                                   */
   int32_t Cin, Cout;      /* logical channels (Cout before pixel shuffle)                   */
@@ -154,6 +161,11 @@ int32_t vcm_se_partial_count(int64_t hw);
 int vcm_se_scale(const void* x, float* partial, const float* w1, const float* w2, float* scale,
                  int32_t N, int64_t hw, int32_t C, int32_t Cmid, int32_t cstride, int32_t dtype,
                  void* stream);
+/* the same from channel sums written by a VCM_CONV_SE_SUM conv (N = 1): rows of [C] floats, added in index
+ * order; rows = vcm_conv2d_se_sum_rows(d) of that conv (0: the conv cannot produce them, use vcm_se_scale) */
+int32_t vcm_conv2d_se_sum_rows(const vcm_conv_desc* d);
+int vcm_se_scale_from_sums(const float* sums, int32_t rows, const float* w1, const float* w2, float* scale,
+                           int64_t hw, int32_t C, int32_t Cmid, void* stream);
 
 /* ---- motion glue (fp32 always: flow fields and SpyNet image pyramids) ------------------
  * F.avg_pool2d(x,2,2)            video_net.py:131-133

@@ -377,6 +377,36 @@ def test_conv_rows_engine_is_taken_and_equals_the_halo_engine(B16, rows_engine_s
     assert bool(((got - want).abs() <= 0.01 * want.abs() + 0.02).all())
 
 
+@pytest.mark.parametrize("shape", [(64, 64, 160, 128), (32, 32, 304, 1024), (64, 32, 304, 1024), (64, 64, 37, 53),
+                                   (128, 128, 160, 128)])
+def test_conv_fused_se_channel_sums(B16, rows_engine_small_images, shape):
+    """VCM_CONV_SE_SUM: the SELayer mean out of the producing conv's epilogue (halo and row engines) gives the
+    scales of the stand-alone kernel (other summation order: 1e-5); ragged tiles / wide N tiles report
+    'not available' and the caller keeps the stand-alone kernel."""
+    Ci, C, H, W = shape
+    g = torch.Generator(device="cpu").manual_seed(31)
+    dev, bf = "cuda:0", torch.bfloat16
+    x = torch.randn((1, Ci, H, W), generator=g).to(dev).to(bf)
+    w = (torch.randn((C, Ci, 3, 3), generator=g) / (Ci * 9) ** 0.5).to(dev)
+    b = torch.randn((C,), generator=g).to(dev)
+    w1 = (torch.randn((C // 16, C), generator=g) / 8).to(dev)
+    w2 = torch.randn((C, C // 16), generator=g).to(dev)
+    pc = B16.pack_conv(w, b)
+    x1, sums = B16.conv(view_of(x.float(), dtype=bf), pc, se_sums=True)
+    want_sums = (H % 16 == 0 and W % 8 == 0 and C <= 64)
+    assert (sums is not None) == want_sums, (shape, None if sums is None else tuple(sums.shape))
+    ref_out = ref_conv(x.float(), w.to(bf).float(), b, 1, None, None, False, None, None, None)
+    assert bool(((nchw(x1) - ref_out).abs() <= 0.01 * ref_out.abs() + 0.02).all())
+    if sums is None:
+        return
+    got = B16.se_scale_from_sums(sums, x1, w1, w2)
+    want = B16.se_scale(x1, w1, w2)
+    torch.cuda.synchronize()
+    torch.testing.assert_close(got, want, rtol=1e-5, atol=1e-6)
+    mean = nchw(x1).float().mean(dim=(2, 3))[0]
+    torch.testing.assert_close(sums.sum(0) / (H * W), mean, rtol=1e-4, atol=1e-5)
+
+
 def test_conv_tcgen05_unaligned_views_take_scalar_epilogue(B16):
     """Output / residual views whose channel stride or offset is not a multiple of 8 cannot use the
     16-byte vector epilogue: the tensor-core engine must still take the conv (scalar bf16 epilogue)."""

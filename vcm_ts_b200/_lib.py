@@ -13,7 +13,7 @@ SO = os.environ.get("VCM_B200_SO") or os.path.join(HERE, "libvcmts_b200.so")   #
 
 F32, BF16 = 0, 1
 CONV_PRE_ACT, CONV_POST_ACT, CONV_PIXEL_SHUFFLE = 1, 2, 4
-CONV_RES, CONV_RES_SCALE, CONV_RES2, CONV_OUT2, CONV_SPLIT3, CONV_PDL = 8, 16, 32, 64, 128, 256
+CONV_RES, CONV_RES_SCALE, CONV_RES2, CONV_OUT2, CONV_SPLIT3, CONV_PDL, CONV_SE_SUM = 8, 16, 32, 64, 128, 256, 512
 
 
 class ConvDesc(Structure):
@@ -60,6 +60,8 @@ _PROTOS = {
     "vcm_maxpool2": (c_int, [_P, _P, c_int32, c_int32, c_int32, c_int32, c_int32, c_int32, c_int32, _P]),
     "vcm_se_partial_count": (c_int32, [c_int64]),
     "vcm_se_scale": (c_int, [_P, _P, _P, _P, _P, c_int32, c_int64, c_int32, c_int32, c_int32, c_int32, _P]),
+    "vcm_conv2d_se_sum_rows": (c_int32, [POINTER(ConvDesc)]),
+    "vcm_se_scale_from_sums": (c_int, [_P, c_int32, _P, _P, _P, c_int64, c_int32, c_int32, _P]),
     "vcm_avgpool2": (c_int, [_P, _P, c_int32, c_int32, c_int32, c_int32, c_int32, c_int32, _P]),
     "vcm_flow_up2": (c_int, [_P, _P, c_int32, c_int32, c_int32, c_int32, c_int32, c_float, _P]),
     "vcm_flow_down2": (c_int, [_P, _P, c_int32, c_int32, c_int32, c_int32, c_int32, c_float, _P]),

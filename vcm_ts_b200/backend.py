@@ -94,6 +94,8 @@ class CudaBackend:
         # conv leaves) nor the single-sequence rate (43.4 / 28.9 frames/s with, 43.9 / 28.9 without).
         import os
         self.pdl = os.environ.get("VCM_B200_PDL", "0") == "1"
+        # SELayer means out of the producing conv's epilogue (bf16 tensor-core mode; VCM_B200_FUSED_SE=0: off)
+        self.fused_se_sums = precision == "bf16" and os.environ.get("VCM_B200_FUSED_SE", "1") == "1"
 
     # -- plumbing -------------------------------------------------------------------------
     @property
@@ -160,9 +162,11 @@ class CudaBackend:
 
     # -- convolution ------------------------------------------------------------------------
     def conv(self, x, pc, out=None, stride=1, pre=None, post=None, res=None, res_scale=None,
-             res2=None, ps=False, out_dtype=None, slope2=None, out2=None):
+             res2=None, ps=False, out_dtype=None, slope2=None, out2=None, se_sums=False):
         """Fused conv.  With slope2 set, also stores leaky_relu(y, slope2) to `out2` and returns
-        (y, y_act)."""
+        (y, y_act).  se_sums=True (bf16 tensor-core mode): returns (y, sums) where sums is a float
+        [rows, Cout] tensor of channel sums of y for `se_scale_from_sums`, or None where the engine cannot
+        produce them for this launch (then use `se_scale(y, ...)`)."""
         K = pc.K
         assert x.C == pc.Cin, f"conv input has {x.C} channels, weights expect {pc.Cin}"
         pad = K // 2
@@ -227,12 +231,20 @@ class CudaBackend:
                 check(self.L.vcm_conv2d_tc_fwd(*args), "vcm_conv2d_tc_fwd")
                 self.launches += 2
                 return (out, out2) if slope2 is not None else out
+        sums = None
         if self.precision == "bf16" and pc.w_umma is not None and \
                 self.L.vcm_conv2d_tc_supported(ctypes.byref(d)) == 1:
             if pc.ps != bool(ps):
                 raise RuntimeError("conv weights were packed for ps=%s but the conv is launched with ps=%s"
                                    % (pc.ps, bool(ps)))
             args[2], args[3] = pc.w_umma.data_ptr(), pc.bias_tc.data_ptr()
+            if se_sums and slope2 is None and (x.ptr % 16 == 0) and (out.ptr % 16 == 0) and \
+                    (res is None or res.ptr % 16 == 0):
+                rows = self.L.vcm_conv2d_se_sum_rows(ctypes.byref(d))
+                if rows > 0:
+                    sums = self.empty((rows, pc.Cout), torch.float32)
+                    d.flags |= _lib.CONV_SE_SUM
+                    args[8] = sums.data_ptr()
             rc = self.L.vcm_conv2d_tc_fwd(*args)
             if rc == 2 and not pc.ps:     # e.g. a view whose base is not 16-byte aligned: fp32-FMA engine
                 args[2], args[3] = pc.w.data_ptr(), pc.bias.data_ptr()
@@ -242,6 +254,8 @@ class CudaBackend:
             args[2] = pc.w.data_ptr()
             check(self.L.vcm_conv2d_fwd(*args), "vcm_conv2d_fwd")
         self.launches += 1
+        if se_sums:
+            return out, sums
         return (out, out2) if slope2 is not None else out
 
     # -- layout / elementwise ---------------------------------------------------------------
@@ -303,6 +317,16 @@ class CudaBackend:
                                   scale.data_ptr(), x.N, hw, x.C, w1.shape[0], x.cs, _code(x.dtype),
                                   self.stream), "vcm_se_scale")
         self.launches += 2
+        return scale
+
+    def se_scale_from_sums(self, sums, x, w1, w2):
+        """SELayer scale [1, C] from the channel sums a `conv(..., se_sums=True)` wrote for its output x."""
+        assert x.N == 1 and sums.shape[1] == x.C
+        scale = self.empty((1, x.C), torch.float32)
+        check(self.L.vcm_se_scale_from_sums(sums.data_ptr(), sums.shape[0], w1.data_ptr(), w2.data_ptr(),
+                                            scale.data_ptr(), x.H * x.W, x.C, w1.shape[0], self.stream),
+              "vcm_se_scale_from_sums")
+        self.launches += 1
         return scale
 
     # -- motion glue (fp32) -----------------------------------------------------------------

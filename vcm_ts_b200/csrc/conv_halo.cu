@@ -402,6 +402,8 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       E.scale_smem = G.scale_off ? smem_u32(smem + G.bias_base + G.scale_off) : 0u;
       E.rfull = &rfull[2 * g];
       E.k = 0;
+      E.se_sum = (P.flags & VCM_CONV_SE_SUM) != 0;
+      E.se0 = E.se1 = 0.f;
       E.leader = (q == 0 && lane == 0);
       E.bar = 1 + g;
       const bool has_res = P.flags & (VCM_CONV_RES | VCM_CONV_RES_SCALE);
@@ -454,6 +456,10 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         else EPI_TMA(32);
 #undef EPI_TMA
       }
+      if (E.se_sum) {
+        if (G.sw == 64) epi_tma_write_se_sums<64>(E, reinterpret_cast<float*>(P.y2), warp - 4, lane);
+        else epi_tma_write_se_sums<32>(E, reinterpret_cast<float*>(P.y2), warp - 4, lane);
+      }
       if (E.leader) tma_store_wait_all();
     } else {
     int local = 0;
@@ -505,10 +511,10 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
 
 // ---------------------------------------------------------------------------------- host
 int vcm_conv_halo_launch(const vcm_conv_desc* d, const ConvParams& P, const void* x, const void* w_umma,
-                         cudaStream_t stream) {
+                         cudaStream_t stream, int* se_rows) {
   if (P.stride != 1) return 3;
   {   // narrow 3x3 layers on large images: output rows stacked along N (conv_rows.cu)
-    const int rc = vcm_conv_rows_launch(d, P, x, w_umma, stream);
+    const int rc = vcm_conv_rows_launch(d, P, x, w_umma, stream, se_rows);
     if (rc != 3) return rc;
   }
   EncodeTiledFn enc = get_encode_fn();
@@ -616,6 +622,19 @@ int vcm_conv_halo_launch(const vcm_conv_desc* d, const ConvParams& P, const void
   G.idesc = make_idesc_bf16(128, G.bn);
   G.epi_bw = tc_epilogue_bw(d, G.bn);
 
+  {   // VCM_CONV_SE_SUM: one tile = one whole 128-pixel x Cout block of one image
+    const bool se_ok = G.tma_epi == 1 && G.nsub == 1 && G.n_tiles == 1 && P.N == 1 && !G.ps_q4 &&
+                       !(P.flags & VCM_CONV_OUT2) && P.Wo % HTW == 0 && P.Ho % (HTH * G.mh) == 0;
+    const int grid_q = G.num_items < num_sms() ? G.num_items : num_sms();
+    if (se_rows) {
+      *se_rows = se_ok ? 8 * grid_q : 0;
+      return 0;
+    }
+    if ((P.flags & VCM_CONV_SE_SUM) && !se_ok) {
+      vcm_set_error("vcm_conv_halo_launch: VCM_CONV_SE_SUM is not available for this launch (see vcm_conv2d_se_sum_rows)");
+      return 1;
+    }
+  }
   CUtensorMap tmA, tmB;
   {
     cuuint64_t dims[4] = {(cuuint64_t)(P.Cin + (G.split ? 2 * G.pstride : 0)), (cuuint64_t)P.W, (cuuint64_t)P.H,

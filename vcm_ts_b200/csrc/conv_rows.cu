@@ -267,6 +267,8 @@ conv_rows_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     E.scale_smem = G.scale_off ? smem_u32(smem + G.bias_base + G.scale_off) : 0u;
     E.rfull = &rfull[2 * g];
     E.k = 0;
+    E.se_sum = (P.flags & VCM_CONV_SE_SUM) != 0;
+    E.se0 = E.se1 = 0.f;
     E.leader = (q == 0 && lane == 0);
     E.bar = 1 + g;
     const bool has_res = P.flags & (VCM_CONV_RES | VCM_CONV_RES_SCALE);
@@ -295,6 +297,7 @@ conv_rows_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                             h == R - 1 ? &tempty[ab] : nullptr, bias_smem, ok2, n2, oy2, ox2, 0);
       ok = ok2; h = h2; n = n2; oy0 = oy2; ox0 = ox2;
     }
+    if (E.se_sum) epi_tma_write_se_sums<BN>(E, reinterpret_cast<float*>(P.y2), warp - 4, lane);
     if (E.leader) tma_store_wait_all();
     }
   }
@@ -312,7 +315,7 @@ conv_rows_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
 // ---------------------------------------------------------------------------------- host
 // returns 0 ok, 1 error, 3 = shape not taken
 int vcm_conv_rows_launch(const vcm_conv_desc* d, const ConvParams& P, const void* x, const void* w_umma,
-                         cudaStream_t stream) {
+                         cudaStream_t stream, int* se_rows) {
   const char* off_env = getenv("VCM_TC_NO_ROWS");   // read per launch: tests compare the engines in one process
   const bool off = off_env && off_env[0] == '1';
   static const bool no_tma_epi = getenv("VCM_TC_NO_TMA_EPI") && getenv("VCM_TC_NO_TMA_EPI")[0] == '1';
@@ -390,6 +393,18 @@ int vcm_conv_rows_launch(const vcm_conv_desc* d, const ConvParams& P, const void
   if (smem_bytes > SMEM_LIMIT) return 3;
   if (smem_bytes < 120 * 1024) smem_bytes = 120 * 1024;   // one CTA per SM (TMEM is per CTA)
 
+  {   // VCM_CONV_SE_SUM: whole strips of one image through the TMA epilogue
+    const bool se_ok = !G.scalar_epi && P.N == 1 && P.Wo % R_STRIP == 0 && !(P.flags & VCM_CONV_OUT2) &&
+                       (G.bn == 64 || G.bn == 32 || G.bn == 16);
+    if (se_rows) {
+      *se_rows = se_ok ? 8 * num_sms() : 0;
+      return 0;
+    }
+    if ((P.flags & VCM_CONV_SE_SUM) && !se_ok) {
+      vcm_set_error("vcm_conv_rows_launch: VCM_CONV_SE_SUM is not available for this launch (see vcm_conv2d_se_sum_rows)");
+      return 1;
+    }
+  }
   CUtensorMap tmA, tmB, tmY, tmY2, tmR;
   memset(&tmY, 0, sizeof(tmY));
   memset(&tmY2, 0, sizeof(tmY2));

@@ -190,6 +190,7 @@ extern "C" int vcm_conv2d_fwd(const vcm_conv_desc* d, const void* x, const float
   VCM_CHECK_ARG(!(P.flags & VCM_CONV_RES_SCALE) || res_scale, "RES_SCALE without scale");
   VCM_CHECK_ARG(!(P.flags & VCM_CONV_RES2) || res2, "RES2 without tensor");
   VCM_CHECK_ARG(!(P.flags & VCM_CONV_OUT2) || y2, "OUT2 without tensor");
+  VCM_CHECK_ARG(!(P.flags & VCM_CONV_SE_SUM), "VCM_CONV_SE_SUM is a tensor-core engine feature");
   P.y2 = y2;
   P.x = x; P.w = w_packed; P.bias = bias; P.res = res; P.res_scale = res_scale; P.res2 = res2; P.y = y;
   P.cin_chunks = cdiv(P.Cin, BK);

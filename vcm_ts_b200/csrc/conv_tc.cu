@@ -394,6 +394,28 @@ extern "C" int vcm_split_bf16x3(const float* src, void* dst, int64_t npix, int32
   return 0;
 }
 
+static bool force_se_pertap() {
+  static const bool f = getenv("VCM_TC_PERTAP") && getenv("VCM_TC_PERTAP")[0] == '1';
+  return f;
+}
+
+extern "C" int32_t vcm_conv2d_se_sum_rows(const vcm_conv_desc* d) {
+  if (force_se_pertap()) return 0;
+  if (!d || !vcm_conv2d_tc_supported(d) || d->in_dtype != VCM_BF16 || d->out_dtype != VCM_BF16) return 0;
+  ConvParams P;
+  memset(&P, 0, sizeof(P));
+  if (conv_fill_params(d, P) != 0 || P.stride != 1 || (P.flags & VCM_CONV_SPLIT3)) return 0;
+  // 16-byte aligned stand-ins: the epilogue choice looks at pointer alignment; a launch whose real pointers
+  // make another choice fails instead of skipping the sums
+  void* al = reinterpret_cast<void*>((uintptr_t)4096);
+  P.x = al; P.bias = reinterpret_cast<const float*>(al); P.res = al;
+  P.res_scale = reinterpret_cast<const float*>(al); P.res2 = al; P.y = al; P.y2 = al;
+  P.flags |= VCM_CONV_SE_SUM;
+  int rows = 0;
+  const int rc = vcm_conv_halo_launch(d, P, al, al, nullptr, &rows);
+  return rc == 0 ? rows : 0;
+}
+
 extern "C" int vcm_conv2d_tc_fwd(const vcm_conv_desc* d, const void* x, const void* w_umma,
                                  const float* bias, const void* res, const float* res_scale,
                                  const void* res2, void* y, void* y2, void* stream) {
@@ -415,6 +437,8 @@ extern "C" int vcm_conv2d_tc_fwd(const vcm_conv_desc* d, const void* x, const vo
   }
   VCM_CHECK_ARG(((uintptr_t)w_umma & 15) == 0, "weights must be 16-byte aligned");
   P.x = x; P.bias = bias; P.res = res; P.res_scale = res_scale; P.res2 = res2; P.y = y; P.y2 = y2;
+  VCM_CHECK_ARG(!(P.flags & VCM_CONV_SE_SUM) || (y2 && !(P.flags & VCM_CONV_OUT2) && P.stride == 1 && !force_se_pertap()),
+                "VCM_CONV_SE_SUM needs y2 = the sums array, no OUT2, a stride-1 conv on the halo / row engines");
 
   // stride-1 shapes go to the halo-tile engine (conv_halo.cu) unless VCM_TC_PERTAP=1 forces this one
   static const bool force_pertap = getenv("VCM_TC_PERTAP") && getenv("VCM_TC_PERTAP")[0] == '1';
@@ -422,6 +446,7 @@ extern "C" int vcm_conv2d_tc_fwd(const vcm_conv_desc* d, const void* x, const vo
     const int rc = vcm_conv_halo_launch(d, P, x, w_umma, (cudaStream_t)stream);
     if (rc != 3) return rc;
   }
+  VCM_CHECK_ARG(!(P.flags & VCM_CONV_SE_SUM), "VCM_CONV_SE_SUM: this shape runs on the per-tap engine, which has no fused sums");
 
   EncodeTiledFn enc = get_encode_fn();
   VCM_CHECK_ARG(enc != nullptr, "cuTensorMapEncodeTiled unavailable");

@@ -447,3 +447,17 @@ extern "C" int vcm_se_scale(const void* x, float* partial, const float* w1, cons
   VCM_CHECK_LAUNCH();
   return 0;
 }
+
+extern "C" int vcm_se_scale_from_sums(const float* sums, int32_t rows, const float* w1, const float* w2,
+                                      float* scale, int64_t hw, int32_t C, int32_t Cmid, void* stream) {
+  VCM_CHECK_ARG(sums && w1 && w2 && scale && rows > 0 && hw > 0 && C > 0 && Cmid > 0, "bad argument");
+  cudaStream_t s = (cudaStream_t)stream;
+  if (C % 4 == 0 && SE_FC_THREADS % (C / 4) == 0 && ((uintptr_t)sums & 15) == 0) {
+    se_fc_striped_kernel<<<1, SE_FC_THREADS, (4 * SE_FC_THREADS + C + Cmid) * sizeof(float), s>>>(
+        sums, w1, w2, scale, hw, C, Cmid, rows);
+  } else {
+    se_fc_kernel<<<1, 256, (C + Cmid) * sizeof(float), s>>>(sums, w1, w2, scale, hw, C, Cmid, rows);
+  }
+  VCM_CHECK_LAUNCH();
+  return 0;
+}

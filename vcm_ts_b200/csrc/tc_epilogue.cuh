@@ -298,6 +298,8 @@ struct EpiTma {
   uint64_t* rfull;           // [2] residual tile landed in staging tile b
   uint32_t scale_smem;       // shared-window address of a copy of res_scale [N][Cout] (0: read it from global)
   int k;                     // tiles this warpgroup has finished (staging tile k & 1, barrier phase (k >> 1) & 1)
+  bool se_sum;               // VCM_CONV_SE_SUM: keep running per-channel sums of the (bf16-rounded) outputs
+  float se0, se1;            // ... of this lane's channel pair over the rows its warp has produced so far
   bool leader;               // the one thread of the warpgroup that issues TMA operations
   int bar;                   // named barrier of this warpgroup (1 or 2)
 };
@@ -308,6 +310,24 @@ __device__ __forceinline__ void epi_tma_prefetch_res(const EpiTma& E, int k, int
   const int b = k & 1;
   mbar_expect_tx(&E.rfull[b], (uint32_t)(128 * BN * 2));
   tma_load_4d(E.obuf + (uint32_t)b * E.tile_bytes, E.tmR, &E.rfull[b], c, x0, y0, n);
+}
+
+// VCM_CONV_SE_SUM: one row of channel sums per epilogue warp, sums[(cta * 8 + epilogue warp)][BN]; rows of warps
+// without tiles are zero.  The SE FC kernel adds the rows in index order (deterministic).
+template <int BN>
+__device__ __forceinline__ void epi_tma_write_se_sums(const EpiTma& E, float* sums, int warp_e, int lane) {
+  constexpr int PAIRS = BN / 2;
+  float a = E.se0, b = E.se1;
+#pragma unroll
+  for (int o = 16; o >= PAIRS; o >>= 1) {          // lanes l, l + PAIRS, ... hold the same pair over other rows
+    a += __shfl_down_sync(0xffffffffu, a, o);
+    b += __shfl_down_sync(0xffffffffu, b, o);
+  }
+  if (lane < PAIRS) {
+    float* row = sums + ((size_t)blockIdx.x * 8 + (size_t)warp_e) * BN;
+    row[2 * lane] = a;
+    row[2 * lane + 1] = b;
+  }
 }
 
 // One warp's 32 pixels of a 128-pixel x 64-channel tile (wq = TMEM lane quarter = tile rows 32*wq ..).
@@ -419,6 +439,28 @@ __device__ __forceinline__ void epilogue_warp_tma(const ConvParams& P, EpiTma& E
                      "r"(o2.z), "r"(o2.w)
                      : "memory");
       }
+    }
+  }
+  if (E.se_sum) {
+    // SELayer mean fused into the producing conv: the warp's 32 rows of the tile are in shared memory as the
+    // bf16 values that go to HBM; lane l adds up one channel pair over them (row order, fp32).  Tiles are
+    // whole (checked on the host), so every row counts.
+    __syncwarp();
+    constexpr int PAIRS = BN / 2, GROUPS = 32 / PAIRS, RPL = 32 / GROUPS;
+    const int pair = lane % PAIRS;
+    const int r0 = wq * 32 + (lane / PAIRS) * RPL;
+#pragma unroll 8
+    for (int i = 0; i < RPL; ++i) {
+      const int r = r0 + i;
+      const uint32_t swr = BN == 64 ? (uint32_t)(r & 7) : (BN == 32 ? (uint32_t)((r >> 1) & 3) : (uint32_t)((r >> 2) & 1));
+      uint32_t wv;
+      asm volatile("ld.shared.u32 %0, [%1];"
+                   : "=r"(wv)
+                   : "r"(obuf + (uint32_t)r * (uint32_t)(BN * 2) + ((((uint32_t)pair >> 2) ^ swr) << 4) +
+                         ((uint32_t)pair & 3u) * 4u)
+                   : "memory");
+      E.se0 += __uint_as_float(wv << 16);
+      E.se1 += __uint_as_float(wv & 0xffff0000u);
     }
   }
   fence_proxy_async();

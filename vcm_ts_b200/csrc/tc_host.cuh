@@ -106,8 +106,10 @@ inline int tc_epilogue_bw(const vcm_conv_desc* d, int bn) {
 
 // stride-1 halo engine (conv_halo.cu); returns 0 ok, 1 error, 3 = shape not taken (use per-tap)
 struct ConvParams;
+// se_rows != nullptr: query only -- *se_rows = rows of channel sums a VCM_CONV_SE_SUM launch of this shape would
+// write (0 = it cannot), nothing is launched
 int vcm_conv_halo_launch(const vcm_conv_desc* d, const ConvParams& P, const void* x, const void* w_umma,
-                         cudaStream_t stream);
+                         cudaStream_t stream, int* se_rows = nullptr);
 // row-stacked 3x3 engine for Cout = 64 / 32 (conv_rows.cu); same return convention
 int vcm_conv_rows_launch(const vcm_conv_desc* d, const ConvParams& P, const void* x, const void* w_umma,
-                         cudaStream_t stream);
+                         cudaStream_t stream, int* se_rows = nullptr);

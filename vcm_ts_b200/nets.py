@@ -122,8 +122,15 @@ class Graph:
     # ---- video_net.py:149-179: up_dim(x) + conv(x) * se(conv(x))
     def conv_block_residual(self, pre, x, out=None, twin_out=None):
         t = self.conv(pre + ".conv.0", x, post=0.01)
-        x1 = self.conv(pre + ".conv.2", t)
-        s = self.B.se_scale(x1, self.lin(pre + ".conv.3.fc.0.weight"), self.lin(pre + ".conv.3.fc.2.weight"))
+        w1, w2 = self.lin(pre + ".conv.3.fc.0.weight"), self.lin(pre + ".conv.3.fc.2.weight")
+        if getattr(self.B, "fused_se_sums", False):
+            # tensor-core mode: the SE mean comes out of the epilogue of the conv that produces x1 where the
+            # engine can do it (one image, whole tiles); no extra pass over x1
+            x1, sums = self.conv(pre + ".conv.2", t, se_sums=True)
+            s = self.B.se_scale_from_sums(sums, x1, w1, w2) if sums is not None else self.B.se_scale(x1, w1, w2)
+        else:
+            x1 = self.conv(pre + ".conv.2", t)
+            s = self.B.se_scale(x1, w1, w2)
         if twin_out is not None:
             return self.conv_t(pre + ".up_dim", x, twin_out, res=x1, res_scale=s, out=out)
         return self.conv(pre + ".up_dim", x, res=x1, res_scale=s, out=out)
