@@ -198,35 +198,55 @@ __global__ void __launch_bounds__(256) flow_warp8_bf16_kernel(const __nv_bfloat1
   const __nv_bfloat16* b = feat + (int64_t)n * H * W * feat_cs + g * 8;
   int oy[PP];
   int64_t p[PP];
-  float2 uv[PP];
 #pragma unroll
   for (int j = 0; j < PP; ++j) {
     oy[j] = blockIdx.y * (PP * th) + j * th + (pix >> 3);
     p[j] = ((int64_t)n * H + min(oy[j], H - 1)) * W + ox;
-    uv[j] = __ldg(reinterpret_cast<const float2*>(flow + p[j] * flow_cs));
   }
   WarpTaps t[PP];
   uint4 v[PP][4];
+  // The G lanes of a pixel are adjacent.  The coordinate arithmetic (four correctly rounded divisions among ~70
+  // instructions) is done ONCE per (pixel, row) and shuffled to the lanes that need it.  With G a power of two
+  // >= 2 a warp holds 32 / G pixels x PP rows <= 32 tap sets: lane L computes the set of (pixel L % PW, row
+  // L / PW) -- all sets of the warp in one pass instead of one divergent pass per row by every G-th lane
+  // (ncu r02: this kernel is issue-bound, ~350 instructions per warp, 140 of them those two passes).
+  const bool coop = G > 1 && (G & (G - 1)) == 0 && G <= 32;
+  if (coop) {
+    const int PW = 32 / G;                               // pixels per warp
+    const int lane = threadIdx.x & 31;
+    const int wpix0 = (threadIdx.x >> 5) * PW;           // first pixel slot of this warp in the block
+    WarpTaps mine;
+    mine.x0 = mine.y0 = 0; mine.nw = mine.ne = mine.sw = mine.se = 0.f;
+    if (lane < PW * PP) {
+      const int pl = wpix0 + lane % PW, jl = lane / PW;
+      const int oxl = min(blockIdx.x * 8 + (pl & 7), W - 1);
+      const int oyl = min((int)(blockIdx.y * (PP * th) + jl * th + (pl >> 3)), H - 1);
+      const float2 uvl = __ldg(reinterpret_cast<const float2*>(flow + (((int64_t)n * H + oyl) * W + oxl) * flow_cs));
+      mine = warp_taps(uvl.x, uvl.y, oxl, oyl, W, H);
+    }
 #pragma unroll
-  for (int j = 0; j < PP; ++j) {
-    // the G lanes of a pixel are adjacent: one of them does the coordinate arithmetic (four correctly rounded
-    // divisions among ~70 instructions), the others receive the taps by shuffle
-    if (G > 1 && (G & (G - 1)) == 0) {
-      if (g == 0) t[j] = warp_taps(uv[j].x, uv[j].y, ox, min(oy[j], H - 1), W, H);
-      const int src = (threadIdx.x & 31) & ~(G - 1);
-      t[j].x0 = __shfl_sync(0xffffffffu, t[j].x0, src);
-      t[j].y0 = __shfl_sync(0xffffffffu, t[j].y0, src);
-      t[j].nw = __shfl_sync(0xffffffffu, t[j].nw, src);
-      t[j].ne = __shfl_sync(0xffffffffu, t[j].ne, src);
-      t[j].sw = __shfl_sync(0xffffffffu, t[j].sw, src);
-      t[j].se = __shfl_sync(0xffffffffu, t[j].se, src);
+    for (int j = 0; j < PP; ++j) {
+      const int src = (lane / G) + j * PW;
+      t[j].x0 = __shfl_sync(0xffffffffu, mine.x0, src);
+      t[j].y0 = __shfl_sync(0xffffffffu, mine.y0, src);
+      t[j].nw = __shfl_sync(0xffffffffu, mine.nw, src);
+      t[j].ne = __shfl_sync(0xffffffffu, mine.ne, src);
+      t[j].sw = __shfl_sync(0xffffffffu, mine.sw, src);
+      t[j].se = __shfl_sync(0xffffffffu, mine.se, src);
       t[j].x1_ok = t[j].x0 + 1 <= W - 1;
       t[j].y1_ok = t[j].y0 + 1 <= H - 1;
       t[j].x1 = t[j].x1_ok ? t[j].x0 + 1 : W - 1;
       t[j].y1 = t[j].y1_ok ? t[j].y0 + 1 : H - 1;
-    } else {
-      t[j] = warp_taps(uv[j].x, uv[j].y, ox, min(oy[j], H - 1), W, H);
     }
+  } else {
+#pragma unroll
+    for (int j = 0; j < PP; ++j) {
+      const float2 uv = __ldg(reinterpret_cast<const float2*>(flow + p[j] * flow_cs));
+      t[j] = warp_taps(uv.x, uv.y, ox, min(oy[j], H - 1), W, H);
+    }
+  }
+#pragma unroll
+  for (int j = 0; j < PP; ++j) {
     v[j][0] = __ldg(reinterpret_cast<const uint4*>(b + ((int64_t)t[j].y0 * W + t[j].x0) * feat_cs));
     v[j][1] = __ldg(reinterpret_cast<const uint4*>(b + ((int64_t)t[j].y0 * W + t[j].x1) * feat_cs));
     v[j][2] = __ldg(reinterpret_cast<const uint4*>(b + ((int64_t)t[j].y1 * W + t[j].x0) * feat_cs));
