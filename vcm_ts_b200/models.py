@@ -354,11 +354,17 @@ class DMC(CompressionModel):
     def _ctx_buffer(self, rt, N, H, W):
         """[feat32 (32) | context1 (64) | x (3) | zero pad] : recon reads [0,96) in the reference's
         cat order (video_model.py:124,330), the contextual encoder reads [32, 32+Cin_p)."""
-        pad = 13 if rt.B.precision == "bf16" else 1
+        pad = self._ENC_PAD if rt.B.precision == "bf16" else 1
         return self._persist(rt, "ctx", N, H, W, 99 + pad, rt.B.act_dtype)
 
+    # bf16 mode: zero channels after x so that the stride-2 conv1 of the contextual encoder sees 96 = 3 x 32
+    # input channels (context1 64 + x 3 + 29 zeros).  With 13 (80 = 5 x 16 channels) its per-tap engine moved
+    # 45 boxes of 32-byte rows per tile and TMA's per-row cost made it 320 us at 1080p; 27 boxes of 64-byte rows
+    # cost less even with the extra zero bytes.
+    _ENC_PAD = int(os.environ.get("VCM_B200_ENC_PAD", "29"))
+
     def _enc_in_map(self, rt):
-        pad = 13 if rt.B.precision == "bf16" else 0
+        pad = self._ENC_PAD if rt.B.precision == "bf16" else 0
         # buffer order (context1 0..63, x 64..66, pad) -> reference order cat([x, context1])
         return [3 + j for j in range(64)] + [0, 1, 2] + [-1] * pad
 
