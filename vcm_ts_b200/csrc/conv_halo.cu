@@ -31,8 +31,7 @@ using namespace tc;
 namespace {
 
 constexpr int HTW = 8, HTH = 16;
-constexpr int H_THREADS = 384;    // warps 0-3 producers / MMA, warps 4-11 = two epilogue warpgroups
-constexpr int H_THREADS3 = 512;   // W3 variant (bf16 TMA epilogue only): warps 4-15 = three epilogue warpgroups
+constexpr int H_THREADS = 384;
 constexpr int H_MAX_A = 6, H_MAX_B = 12, H_MAX_ACC = 4;
 
 struct HaloGeom {
@@ -51,7 +50,6 @@ struct HaloGeom {
   int epi_base, bar_base, bias_base, epi_bw;
   int scale_off;   // byte offset (from bias_base) of the shared-memory copy of res_scale, 0 = none
   int tma_epi;   // bf16 tiles leave through TMA stores (tc_epilogue.cuh epilogue_warp_tma)
-  int nwg;       // epilogue warpgroups at work: 3 with the TMA epilogue where shared memory allows, else 2
   int sw, nsub;  // tma_epi == 1: an N tile of bn columns leaves as nsub sub-tiles of sw (64 / 32) channels
   int ps_q4;     // PixelShuffle through TMA: Cout / 4 (sub-tiles go to the strided positions of one sub-pixel phase), else 0
   uint32_t idesc;
@@ -234,10 +232,8 @@ __device__ __forceinline__ void mma_role_split(const HaloGeom& G, const HaloBars
   }
 }
 
-// W3: the variant with three epilogue warpgroups.  It contains only the bf16 TMA-store epilogue, whose register
-// need fits the 128 registers per thread that 512 threads leave (the vector / fp32 / scalar epilogues do not).
-template <int CHUNK, bool W3>
-__global__ void __launch_bounds__(W3 ? H_THREADS3 : H_THREADS, 1)
+template <int CHUNK>
+__global__ void __launch_bounds__(H_THREADS, 1)
 conv_halo_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                  const __grid_constant__ CUtensorMap tmY, const __grid_constant__ CUtensorMap tmY2,
                  const __grid_constant__ CUtensorMap tmR, const ConvParams P, const HaloGeom G) {
@@ -254,8 +250,8 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   uint64_t* bempty = bfull + H_MAX_B;
   uint64_t* tfull = bempty + H_MAX_B;
   uint64_t* tempty = tfull + H_MAX_ACC;
-  uint64_t* rfull = tempty + H_MAX_ACC;      // [3][2]: residual tile b of epilogue warpgroup g has landed
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(rfull + 6);
+  uint64_t* rfull = tempty + H_MAX_ACC;      // [2][2]: residual tile b of epilogue warpgroup g has landed
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(rfull + 4);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int sp_tiles = G.tiles_x * G.tiles_y;
@@ -267,7 +263,7 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     for (int s = 0; s < H_MAX_A; ++s) { mbar_init(&afull[s], 1); mbar_init(&aempty[s], 1); }
     for (int s = 0; s < H_MAX_B; ++s) { mbar_init(&bfull[s], 1); mbar_init(&bempty[s], 1); }
     for (int a = 0; a < H_MAX_ACC; ++a) { mbar_init(&tfull[a], 1); mbar_init(&tempty[a], 4); }
-    for (int r = 0; r < 6; ++r) mbar_init(&rfull[r], 1);
+    for (int r = 0; r < 4; ++r) mbar_init(&rfull[r], 1);
     if (G.tma_epi) {
       prefetch_tmap(&tmY);
       if (G.tma_epi == 1 && (P.flags & VCM_CONV_OUT2)) prefetch_tmap(&tmY2);
@@ -293,7 +289,7 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   pdl_trigger();   // the next kernel of the stream may start its prologue on SMs this grid has left
 
   if (warp < 4) {
-  reg_dec<W3 ? 56 : 72>();
+  reg_dec<72>();
   if (warp == 0) {
     // ============================ activation producer: one halo box per (item, chunk) ==========
     if (lane == 0) {
@@ -374,14 +370,13 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
 #undef HALO_MMA
   }
   } else {
-    reg_inc<W3 ? 152 : 216>();
+    reg_inc<216>();
     // ============ epilogue: warpgroup g (warps 4-7 / 8-11) owns accumulator buffer g ===========
     const int g = (warp - 4) >> 2;
     const int q = warp & 3;   // TMEM lane quarter this warp may access
-    {
     const uint32_t stage = smem_u32(smem + G.epi_base) + (uint32_t)((warp - 4) * EPI_STAGE_FLOATS * 4);
     pdl_wait();   // residuals / SE scales are read and outputs written only after the predecessor finished
-    if (!W3 && G.tma_epi == 2) {
+    if (G.tma_epi == 2) {
       // split-bf16 parity mode (mh == 1): fp32 tiles through TMA stores, one staging buffer per warpgroup
       const uint32_t obuf = smem_u32(smem + G.epi_base) + (uint32_t)(g * EPI_TMA_TILE_BYTES);
       const bool leader = (q == 0 && lane == 0);
@@ -398,7 +393,7 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                               &tfull[ab], acc_phase, &tempty[ab], bias_smem);
       }
       if (leader) tma_store_wait_all();
-    } else if (W3 || G.tma_epi) {
+    } else if (G.tma_epi) {
       // this warpgroup's k-th tile: item local = 2 * (k / mh) + g, half h = k % mh
       EpiTma E;
       E.tmY = &tmY; E.tmY2 = &tmY2; E.tmR = &tmR;
@@ -416,7 +411,7 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       const int per_item = G.mh * G.nsub;
       // -> tensor-map coordinates (sx, sy, cs) of the tile, its first GEMM column cb and TMEM column offset tc
       auto tile = [&](int k, int& n, int& sy, int& sx, int& cs, int& cb, int& tc, bool& first, bool& last) -> bool {
-        const int loc = G.nwg * (k / per_item) + g;
+        const int loc = 2 * (k / per_item) + g;
         const int rem = k % per_item;
         const int h = rem / G.nsub, sub = rem - h * G.nsub;
         const int item = blockIdx.x + loc * gridDim.x;
@@ -450,7 +445,7 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         int n2, sy2, sx2, cs2, cb2, tc2;
         bool f2, l2;
         const bool ok2 = has_res && tile(k + 1, n2, sy2, sx2, cs2, cb2, tc2, f2, l2);   // whose residual is requested next
-        const int loc = G.nwg * (k / per_item) + g;
+        const int loc = 2 * (k / per_item) + g;
         const int ab = loc % G.nacc;
         const uint32_t acc_phase = (uint32_t)(loc / G.nacc) & 1u;
         const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(ab * G.mh * G.bn + tc);
@@ -462,8 +457,8 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
 #undef EPI_TMA
       }
       if (E.se_sum) {
-        if (G.sw == 64) epi_tma_write_se_sums<64>(E, reinterpret_cast<float*>(P.y2), 4 * G.nwg, warp - 4, lane);
-        else epi_tma_write_se_sums<32>(E, reinterpret_cast<float*>(P.y2), 4 * G.nwg, warp - 4, lane);
+        if (G.sw == 64) epi_tma_write_se_sums<64>(E, reinterpret_cast<float*>(P.y2), warp - 4, lane);
+        else epi_tma_write_se_sums<32>(E, reinterpret_cast<float*>(P.y2), warp - 4, lane);
       }
       if (E.leader) tma_store_wait_all();
     } else {
@@ -500,7 +495,6 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             epilogue_thread_scalar<bf>(P, G.bn, n, oy, ox, cbase, taddr, wait, acc_phase, release);
         }
       }
-    }
     }
     }
   }
@@ -579,18 +573,7 @@ int vcm_conv_halo_launch(const vcm_conv_desc* d, const ConvParams& P, const void
       (!(P.flags & VCM_CONV_RES_SCALE) || ((uintptr_t)P.res_scale & 15) == 0))
     G.tma_epi = 2;   // fp32 sub-tiles of 32 channels (epilogue_warp_tma_f32)
   auto a_stage = [&](int mh) { return (G.split ? 3 : 1) * round_up(G.hw * (HTH * mh + P.K - 1) * chunk * 2, 1024); };
-  // A third epilogue warpgroup (+2 staging tiles) where the layer is paced by the epilogue warps -- the 1x1 convs
-  // and everything else with little MMA work per output byte -- and shared memory has the room: resident
-  // weights must still leave 3 activation stages (with 2, the 3x3 64->64 layers got slower, not faster).
-  // Measured, same box: 1x1 64->64 at 1088x1920 104 -> 91 us (5.9 TB/s), P-frame 20.51 -> 20.14 ms.
-  static const int nwg_env = getenv("VCM_TC_NWG") ? atoi(getenv("VCM_TC_NWG")) : 3;
-  G.nwg = 2;
-  if (G.tma_epi == 1 && nwg_env >= 3) {
-    const int w_bytes = G.n_tiles == 1 ? slabs * G.b_slot_bytes : 1 << 30;
-    const int room = SMEM_LIMIT - 1024 - 512 - bias_bytes - 6 * EPI_TMA_TILE_BYTES;
-    if (w_bytes + 3 * a_stage(1) <= room || (w_bytes > room && 3 * a_stage(2) + 6 * G.b_slot_bytes <= room)) G.nwg = 3;
-  }
-  const int epi_bytes = G.tma_epi == 1 ? G.nwg * 2 * EPI_TMA_TILE_BYTES : EPI_STAGE_BYTES;
+  const int epi_bytes = G.tma_epi == 1 ? EPI_TMA_BYTES : EPI_STAGE_BYTES;
   const int budget = SMEM_LIMIT - 1024 - 512 - bias_bytes - epi_bytes;   // alignment slack, barriers, bias, staging
 
   // resident weights if they leave room for >= 3 activation stages
@@ -644,7 +627,7 @@ int vcm_conv_halo_launch(const vcm_conv_desc* d, const ConvParams& P, const void
                        !(P.flags & VCM_CONV_OUT2) && P.Wo % HTW == 0 && P.Ho % (HTH * G.mh) == 0;
     const int grid_q = G.num_items < num_sms() ? G.num_items : num_sms();
     if (se_rows) {
-      *se_rows = se_ok ? 4 * G.nwg * grid_q : 0;
+      *se_rows = se_ok ? 8 * grid_q : 0;
       return 0;
     }
     if ((P.flags & VCM_CONV_SE_SUM) && !se_ok) {
@@ -725,17 +708,17 @@ int vcm_conv_halo_launch(const vcm_conv_desc* d, const ConvParams& P, const void
   int smem_bytes = G.bias_base + bias_bytes + 1024;
   if (smem_bytes < 120 * 1024) smem_bytes = 120 * 1024;   // one CTA per SM (TMEM is per CTA)
   const int grid = G.num_items < num_sms() ? G.num_items : num_sms();
-#define LAUNCH_HALO(CH, W3)                                                                              \
+#define LAUNCH_HALO(CH)                                                                                  \
   do {                                                                                                   \
     static bool attr_set[MAX_DEVICES] = {false};                                                         \
-    cudaError_t e = ensure_max_smem(conv_halo_kernel<CH, W3>, attr_set, SMEM_LIMIT);                     \
+    cudaError_t e = ensure_max_smem(conv_halo_kernel<CH>, attr_set, SMEM_LIMIT);                         \
     if (e != cudaSuccess) {                                                                              \
       vcm_set_error("vcm_conv_halo_launch: cudaFuncSetAttribute: %s", cudaGetErrorString(e));            \
       return 1;                                                                                          \
     }                                                                                                    \
     cudaLaunchConfig_t cfg = {};                                                                         \
     cfg.gridDim = dim3(grid);                                                                            \
-    cfg.blockDim = dim3(W3 ? H_THREADS3 : H_THREADS);                                                    \
+    cfg.blockDim = dim3(H_THREADS);                                                                      \
     cfg.dynamicSmemBytes = smem_bytes;                                                                   \
     cfg.stream = stream;                                                                                 \
     cudaLaunchAttribute attr[1];                                                                         \
@@ -743,17 +726,11 @@ int vcm_conv_halo_launch(const vcm_conv_desc* d, const ConvParams& P, const void
     attr[0].val.programmaticStreamSerializationAllowed = 1;                                              \
     cfg.attrs = attr;                                                                                    \
     cfg.numAttrs = (P.flags & VCM_CONV_PDL) ? 1 : 0;                                                     \
-    cudaLaunchKernelEx(&cfg, conv_halo_kernel<CH, W3>, tmA, tmB, tmY, tmY2, tmR, P, G);                  \
+    cudaLaunchKernelEx(&cfg, conv_halo_kernel<CH>, tmA, tmB, tmY, tmY2, tmR, P, G);                      \
   } while (0)
-  if (G.nwg == 3) {
-    if (chunk == 64) LAUNCH_HALO(64, true);
-    else if (chunk == 32) LAUNCH_HALO(32, true);
-    else LAUNCH_HALO(16, true);
-  } else {
-    if (chunk == 64) LAUNCH_HALO(64, false);
-    else if (chunk == 32) LAUNCH_HALO(32, false);
-    else LAUNCH_HALO(16, false);
-  }
+  if (chunk == 64) LAUNCH_HALO(64);
+  else if (chunk == 32) LAUNCH_HALO(32);
+  else LAUNCH_HALO(16);
 #undef LAUNCH_HALO
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) {

@@ -297,7 +297,7 @@ conv_rows_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                             h == R - 1 ? &tempty[ab] : nullptr, bias_smem, ok2, n2, oy2, ox2, 0);
       ok = ok2; h = h2; n = n2; oy0 = oy2; ox0 = ox2;
     }
-    if (E.se_sum) epi_tma_write_se_sums<BN>(E, reinterpret_cast<float*>(P.y2), 8, warp - 4, lane);
+    if (E.se_sum) epi_tma_write_se_sums<BN>(E, reinterpret_cast<float*>(P.y2), warp - 4, lane);
     if (E.leader) tma_store_wait_all();
     }
   }

@@ -312,10 +312,10 @@ __device__ __forceinline__ void epi_tma_prefetch_res(const EpiTma& E, int k, int
   tma_load_4d(E.obuf + (uint32_t)b * E.tile_bytes, E.tmR, &E.rfull[b], c, x0, y0, n);
 }
 
-// VCM_CONV_SE_SUM: one row of channel sums per epilogue warp, sums[(cta * wpc + epilogue warp)][BN]; rows of warps
+// VCM_CONV_SE_SUM: one row of channel sums per epilogue warp, sums[(cta * 8 + epilogue warp)][BN]; rows of warps
 // without tiles are zero.  The SE FC kernel adds the rows in index order (deterministic).
 template <int BN>
-__device__ __forceinline__ void epi_tma_write_se_sums(const EpiTma& E, float* sums, int wpc, int warp_e, int lane) {
+__device__ __forceinline__ void epi_tma_write_se_sums(const EpiTma& E, float* sums, int warp_e, int lane) {
   constexpr int PAIRS = BN / 2;
   float a = E.se0, b = E.se1;
 #pragma unroll
@@ -324,7 +324,7 @@ __device__ __forceinline__ void epi_tma_write_se_sums(const EpiTma& E, float* su
     b += __shfl_down_sync(0xffffffffu, b, o);
   }
   if (lane < PAIRS) {
-    float* row = sums + ((size_t)blockIdx.x * (size_t)wpc + (size_t)warp_e) * BN;
+    float* row = sums + ((size_t)blockIdx.x * 8 + (size_t)warp_e) * BN;
     row[2 * lane] = a;
     row[2 * lane + 1] = b;
   }
