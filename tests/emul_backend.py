@@ -23,6 +23,8 @@ class EmulBackend:
         self.launches = 0
         # "twin": fp32 math but the bf16-mode graph (activated twins instead of pre-activations)
         self.use_twin = precision != "fp32"
+        # the bf16-mode graph also takes the SELayer means out of the producing conv (VCM_CONV_SE_SUM)
+        self.fused_se_sums = self.use_twin
         self.tc_like = []      # (name-less) record of convs that asked for a pre-activation
 
     def new(self, N, H, W, C, dtype=None, zero=False):
@@ -53,7 +55,18 @@ class EmulBackend:
         v.dense().copy_(t_nchw.permute(0, 2, 3, 1).to(v.dtype))
 
     def conv(self, x, pc, out=None, stride=1, pre=None, post=None, res=None, res_scale=None,
-             res2=None, ps=False, out_dtype=None, slope2=None, out2=None):
+             res2=None, ps=False, out_dtype=None, slope2=None, out2=None, se_sums=False):
+        if se_sums:
+            # contract of VCM_CONV_SE_SUM: rows of per-"warp" channel sums of the output that add up to the
+            # channel totals, or None where the engine has no fused sums (here: as the engines, above 64 channels)
+            assert slope2 is None
+            y = self.conv(x, pc, out=out, stride=stride, pre=pre, post=post, res=res, res_scale=res_scale,
+                          res2=res2, ps=ps, out_dtype=out_dtype)
+            if y.N != 1 or y.C > 64:
+                return y, None
+            t = self._nchw(y)[0].reshape(y.C, -1)
+            parts = torch.stack([c.sum(dim=1) for c in torch.chunk(t, 8, dim=1)])
+            return y, parts.contiguous()
         assert x.C == pc.Cin
         if pre is not None:
             self.tc_like.append((pc.K, pc.Cin, pc.Cout))
@@ -121,6 +134,10 @@ class EmulBackend:
 
     def se_scale(self, x, w1, w2):
         m = torch.mean(self._nchw(x), dim=(-1, -2))
+        return torch.sigmoid(F.linear(F.relu(F.linear(m, w1)), w2)).contiguous()
+
+    def se_scale_from_sums(self, sums, x, w1, w2):
+        m = (sums.sum(dim=0) / float(x.H * x.W))[None]
         return torch.sigmoid(F.linear(F.relu(F.linear(m, w1)), w2)).contiguous()
 
     def avgpool(self, x, out=None):
